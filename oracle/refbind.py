@@ -1,0 +1,205 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes binding over oracle/_ref/libglref*.so (the unmodified
+reference compiled by oracle/Makefile) and oracle/libgloracle.so (the plain-C restatement).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product package (xlayer_prover_b200) never does.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+P = 0xFFFFFFFF00000001
+u64p = C.POINTER(C.c_uint64)
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    assert a.dtype == np.uint64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(u64p)
+
+
+class _Lib:
+    """Common face of the reference build (prefix ref_) and the C port (prefix orc_)."""
+
+    def __init__(self, path, prefix):
+        self.path = path
+        self.lib = C.CDLL(path)
+        self.prefix = prefix
+        L = self.lib
+        g = lambda n: getattr(L, prefix + n)
+        u64, i32, u32 = C.c_uint64, C.c_int, C.c_uint32
+        sig = {
+            "add": (u64, [u64, u64]), "sub": (u64, [u64, u64]), "mul": (u64, [u64, u64]),
+            "to_u64": (u64, [u64]), "w": (u64, [u32]), "shift": (u64, []),
+            "canonicalize": (None, [u64p, u64]),
+            "ntt": (i32, [u64p, u64p, u64, u64, u64, u64, i32, i32]),
+            "extend_pol": (i32, [u64p, u64p, u64, u64, u64, u64p, u64, u64]),
+            "hash_full_result": (None, [u64p, u64p]),
+            "hash_full_result_seq": (None, [u64p, u64p]),
+            "linear_hash": (None, [u64p, u64p, u64]),
+            "linear_hash_rows": (None, [u64p, u64p, u64, u64]),
+            "merkletree": (None, [u64p, u64p, u64, u64, i32, u64]),
+            "merkletree_batch": (None, [u64p, u64p, u64, u64, u64, i32, u64]),
+            "tree_num_elements": (u64, [u64]),
+            "max_threads": (i32, []), "set_threads": (None, [i32]),
+            "commit": (i32, [u64p, u64p, u64p, u64, u64, u64, u64p, C.POINTER(C.c_double)]),
+        }
+        for name, (res, args) in sig.items():
+            f = g(name)
+            f.restype, f.argtypes = res, args
+            setattr(self, "_" + name, f)
+
+    # ---- scalars
+    def add(self, a, b): return self._add(a, b)
+    def sub(self, a, b): return self._sub(a, b)
+    def mul(self, a, b): return self._mul(a, b)
+    def to_u64(self, a): return self._to_u64(a)
+    def w(self, k): return self._w(k)
+    def shift(self): return self._shift()
+    def max_threads(self): return self._max_threads()
+    def set_threads(self, n): self._set_threads(n)
+
+    def canonical(self, a):
+        out = np.ascontiguousarray(a, dtype=np.uint64).copy()
+        self._canonicalize(_ptr(out.reshape(-1)), out.size)
+        return out
+
+    # ---- NTT
+    def ntt(self, src, inverse=False, extend=False, nphase=3, nblock=1):
+        src = np.ascontiguousarray(src, dtype=np.uint64)
+        a = src.reshape(src.shape[0], -1) if src.ndim > 1 else src.reshape(-1, 1)
+        size, ncols = a.shape
+        dst = np.zeros_like(a)
+        if size and ncols:
+            rc = self._ntt(_ptr(dst), _ptr(a.copy()), size, ncols, nphase, nblock, int(inverse), int(extend))
+            if rc:
+                raise ValueError("reference ntt rc=%d" % rc)
+        return self.canonical(dst).reshape(src.shape)
+
+    def extend_pol(self, inp, n_ext, nphase=3, nblock=1):
+        inp = np.ascontiguousarray(inp, dtype=np.uint64)
+        n, ncols = inp.shape
+        out = np.zeros((n_ext, ncols), dtype=np.uint64)
+        buf = np.zeros((n_ext, ncols), dtype=np.uint64)
+        self._extend_pol(_ptr(out), _ptr(inp.copy()), n_ext, n, ncols, _ptr(buf), nphase, nblock)
+        return self.canonical(out)
+
+    # ---- Poseidon
+    def hash_full_result(self, x, seq=False):
+        x = np.ascontiguousarray(x, dtype=np.uint64)
+        out = np.zeros(12, dtype=np.uint64)
+        (self._hash_full_result_seq if seq else self._hash_full_result)(_ptr(out), _ptr(x))
+        return self.canonical(out)
+
+    def linear_hash(self, x):
+        x = np.ascontiguousarray(x, dtype=np.uint64).reshape(-1)
+        out = np.zeros(4, dtype=np.uint64)
+        self._linear_hash(_ptr(out), _ptr(x) if x.size else None, x.size)
+        return self.canonical(out)
+
+    def linear_hash_rows(self, x):
+        x = np.ascontiguousarray(x, dtype=np.uint64)
+        nrows, ncols = x.shape
+        out = np.zeros((nrows, 4), dtype=np.uint64)
+        self._linear_hash_rows(_ptr(out), _ptr(x) if x.size else None, ncols, nrows)
+        return self.canonical(out)
+
+    def merkletree(self, x, nrows=None, ncols=None, nthreads=0):
+        if x is not None:
+            x = np.ascontiguousarray(x, dtype=np.uint64)
+            nrows, ncols = x.shape
+        tree = np.zeros(self._tree_num_elements(nrows) if nrows else 0, dtype=np.uint64)
+        if nrows:
+            self._merkletree(_ptr(tree), _ptr(x) if (x is not None and x.size) else None, ncols, nrows, nthreads, 1)
+        return self.canonical(tree)
+
+    def merkletree_batch(self, x, batch, nthreads=0):
+        x = np.ascontiguousarray(x, dtype=np.uint64)
+        nrows, ncols = x.shape
+        tree = np.zeros(self._tree_num_elements(nrows), dtype=np.uint64)
+        self._merkletree_batch(_ptr(tree), _ptr(x), ncols, nrows, batch, nthreads, 1)
+        return self.canonical(tree)
+
+    def commit(self, inp, n_ext):
+        """extendPol + merkletree as Starks::genProof step 1 runs them; returns (ext, tree, (t_lde, t_merkle))."""
+        inp = np.ascontiguousarray(inp, dtype=np.uint64)
+        n, ncols = inp.shape
+        out = np.zeros((n_ext, ncols), dtype=np.uint64)
+        buf = np.zeros((n_ext, ncols), dtype=np.uint64)
+        tree = np.zeros(self._tree_num_elements(n_ext), dtype=np.uint64)
+        secs = (C.c_double * 2)()
+        self._commit(_ptr(out), _ptr(tree), _ptr(inp), n, n_ext, ncols, _ptr(buf), secs)
+        return out, tree, (secs[0], secs[1])
+
+
+class RefLib(_Lib):
+    """The compiled reference, plus the entry points only it has (MerkleTreeGL, root, ...)."""
+
+    def __init__(self, path):
+        super().__init__(path, "ref_")
+        L = self.lib
+        u64, vp = C.c_uint64, C.c_void_p
+        L.ref_is_avx512.restype = C.c_int
+        L.ref_root.restype, L.ref_root.argtypes = u64, [u64, C.c_uint32, u64]
+        L.ref_reverse_permutation.restype, L.ref_reverse_permutation.argtypes = None, [u64p, u64p, u64, u64, u64, u64]
+        L.ref_ntt_maxsize.restype, L.ref_ntt_maxsize.argtypes = C.c_int, [u64p, u64p, u64, u64, u64, C.c_int]
+        L.ref_merkletree_seq.restype, L.ref_merkletree_seq.argtypes = None, [u64p, u64p, u64, u64, C.c_int, u64]
+        L.ref_mt_new.restype, L.ref_mt_new.argtypes = vp, [u64, u64, u64p]
+        L.ref_mt_map.restype, L.ref_mt_map.argtypes = vp, [u64p]
+        L.ref_mt_free.restype, L.ref_mt_free.argtypes = None, [vp]
+        L.ref_mt_merkelize.restype, L.ref_mt_merkelize.argtypes = None, [vp]
+        L.ref_mt_nodes.restype, L.ref_mt_nodes.argtypes = u64p, [vp]
+        L.ref_mt_num_elements.restype, L.ref_mt_num_elements.argtypes = u64, [vp]
+        L.ref_mt_proof_size.restype, L.ref_mt_proof_size.argtypes = u64, [vp]
+        L.ref_mt_get_root.restype, L.ref_mt_get_root.argtypes = None, [vp, u64p]
+        L.ref_mt_get_group_proof.restype, L.ref_mt_get_group_proof.argtypes = None, [vp, u64p, u64]
+
+    def is_avx512(self): return bool(self.lib.ref_is_avx512())
+    def root(self, max_size, domain_pow, idx): return self.lib.ref_root(max_size, domain_pow, idx)
+
+    def merkle_tree_gl(self, source):
+        """MerkleTreeGL(height,width,source).merkelize(); returns (nodes, root, proof_size, get_group_proof)."""
+        source = np.ascontiguousarray(source, dtype=np.uint64)
+        h, w = source.shape
+        L = self.lib
+        mt = L.ref_mt_new(h, w, _ptr(source))
+        L.ref_mt_merkelize(mt)
+        n = L.ref_mt_num_elements(mt)
+        nodes = np.ctypeslib.as_array(L.ref_mt_nodes(mt), shape=(n,)).copy()
+        root = np.zeros(4, dtype=np.uint64)
+        L.ref_mt_get_root(mt, _ptr(root))
+        psize = L.ref_mt_proof_size(mt)
+        proofs = {}
+
+        def group_proof(idx):
+            pr = np.zeros(w + 4 * psize, dtype=np.uint64)
+            L.ref_mt_get_group_proof(mt, _ptr(pr), idx)
+            return self.canonical(pr)
+        return self.canonical(nodes), self.canonical(root), psize, group_proof
+
+
+_cache = {}
+
+
+def reference(avx512=False):
+    """The compiled reference (oracle/_ref); None when it has not been built."""
+    name = "libglref512.so" if avx512 else "libglref.so"
+    path = os.path.join(HERE, "_ref", name)
+    if path not in _cache:
+        _cache[path] = RefLib(path) if os.path.exists(path) else None
+    return _cache[path]
+
+
+def port():
+    """The plain-C restatement (oracle/gl_oracle.c); None when not built."""
+    path = os.path.join(HERE, "libgloracle.so")
+    if path not in _cache:
+        _cache[path] = _Lib(path, "orc_") if os.path.exists(path) else None
+    return _cache[path]
+
+
+def best():
+    """Reference when built, else the port (header of DESIGN.md: parity is pinned on the reference)."""
+    return reference() or port()
