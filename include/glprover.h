@@ -1,0 +1,121 @@
+/* glprover.h -- C ABI of libglprover.so, the B200 (sm_100a) implementation of the zkEVM prover's
+ * STARK-commitment hot path: Goldilocks NTT / INTT / extendPol + Poseidon-Goldilocks linear_hash / merkletree.
+ *
+ * The reference (okx/xlayer-prover) has no FFI layer on this path: Starks::genProof calls two C++ classes
+ * directly.  The drop-in is therefore source level -- include/ntt_goldilocks.hpp and include/merkleTreeGL.hpp
+ * keep the reference's class and method signatures and forward here.  Every entry point
+ * below names the reference function it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *  - Field elements are raw uint64_t, the same bytes as Goldilocks::Element{uint64_t fe}
+ *    (src/goldilocks/src/goldilocks_base_field.hpp:24-27).  Inputs may be non-canonical (>= p);
+ *    every output is canonical, i.e. already passed through Goldilocks::toU64
+ *    (src/goldilocks/src/goldilocks_base_field_tools.hpp:146-163).
+ *  - Matrices are row-major, element (row i, column c) at base[i*pitch + c], exactly the reference layout
+ *    (src/goldilocks/src/ntt_goldilocks.cpp:95-109).
+ *  - Every data pointer may be a device pointer or a host pointer (pageable or pinned); the library asks
+ *    the driver which (cudaPointerGetAttributes) and stages host data through the GPU.  There is NO CPU
+ *    implementation behind this ABI: without a usable CUDA device glp_init fails with GLP_E_CUDA.
+ *  - Every function returns 0 or a negative GLP_E_* code; glp_last_error() gives the thread's last message.
+ *  - A glp_ctx owns one device, one stream, its twiddle tables and scratch; it is not thread-safe, use one
+ *    per host thread (the reference's NTT_Goldilocks objects are per-thread too, fri/friProve.cpp:93-105).
+ */
+#ifndef GLPROVER_H
+#define GLPROVER_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GLP_OK 0
+#define GLP_E_ARG (-1)      /* bad argument: NULL, non power-of-two size ...  (reference: assert, ntt_goldilocks.cpp:28) */
+#define GLP_E_DOMAIN (-2)   /* domain larger than 2^32 (reference: std::range_error, ntt_goldilocks.hpp:94-97) */
+#define GLP_E_CUDA (-3)     /* CUDA runtime failure or no device */
+#define GLP_E_OOM (-4)      /* device or pinned-host allocation failed */
+
+typedef struct glp_ctx glp_ctx;
+
+/* ---- lifetime ---- */
+int glp_init(int device, glp_ctx **ctx);              /* binds to CUDA device `device`, creates the stream */
+void glp_destroy(glp_ctx *ctx);
+const char *glp_last_error(void);
+/* Launch on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the context's own. */
+int glp_set_stream(glp_ctx *ctx, void *cuda_stream);
+int glp_synchronize(glp_ctx *ctx);
+/* kernels launched by this context so far (bench.py reports the difference as gpu_launches) */
+uint64_t glp_launch_count(const glp_ctx *ctx);
+/* cap on internal scratch in bytes (0 = default: a quarter of free device memory, at most 16 GiB) */
+int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes);
+
+/* ---- memory helpers (for callers that keep data resident on the device) ---- */
+int glp_device_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr);
+int glp_device_free(glp_ctx *ctx, void *ptr);
+int glp_host_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr);     /* pinned */
+int glp_host_free(glp_ctx *ctx, void *ptr);
+int glp_memcpy(glp_ctx *ctx, void *dst, const void *src, uint64_t bytes);   /* any direction, synchronous */
+int glp_mem_info(glp_ctx *ctx, uint64_t *free_bytes, uint64_t *total_bytes);
+
+/* ---- NTT_Goldilocks (src/goldilocks/src/ntt_goldilocks.{hpp,cpp}) ---- */
+/* NTT_Goldilocks::NTT / INTT (ntt_goldilocks.cpp:166-232, :307-324).
+ * dst[k,:] = sum_i src[i,:] w^(ik); inverse: dst[j,:] = 1/size * sum_k src[k,:] w^(-jk), times shift^j when
+ * `extend` (the reference's INTT(..., extend=true), ntt_goldilocks.cpp:122-135).
+ * size must be a power of two <= 2^32; size == 0 or ncols == 0 is a no-op; dst == NULL or dst == src works
+ * in place.  The reference's buffer/nphase/nblock arguments are performance hints and have no equivalent. */
+int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend);
+/* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352): out[i,c] = P_c(shift * w_ext^i), i < n_ext, where
+ * P_c interpolates in[:,c] on the size-n subgroup.  out may alias in. */
+int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* Same on a column window: reads in[i*in_pitch + c], writes out[i*out_pitch + c], c < ncols.  This is the unit
+ * of the multi-GPU path (each rank extends its own column slice; north_star / SURVEY 8e). */
+int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_pitch, const uint64_t *in, uint64_t in_pitch,
+                           uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305): dst[i, 0:ncols] = src[BR(i), offset_cols : offset_cols+ncols]
+ * (dst rows have ncols words, src rows ncols_all).  With extension > 1 rows whose source index is >= size/extension
+ * are zero-filled.  dst == src permutes in place (requires ncols == ncols_all, offset_cols == 0, extension <= 1). */
+int glp_reverse_permutation(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t offset_cols,
+                            uint64_t ncols, uint64_t ncols_all, uint64_t extension);
+/* NTT_Goldilocks::root(domainPow, idx) = W[domainPow]^idx (ntt_goldilocks.hpp:169-172), canonical. Host only. */
+uint64_t glp_root(uint32_t domain_pow, uint64_t idx);
+
+/* ---- PoseidonGoldilocks (src/goldilocks/src/poseidon_goldilocks.{hpp,cpp}) ---- */
+/* hash_full_result (poseidon_goldilocks.cpp:166-228) on n independent 12-word states; out may alias in. */
+int glp_hash_full_result(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n);
+/* linear_hash (poseidon_goldilocks.cpp:229-265) of every row: out[i*4..+4) = linear_hash(in[i*pitch..+ncols)). */
+int glp_linear_hash_rows(glp_ctx *ctx, uint64_t *out4, const uint64_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows);
+/* merkletree / merkletree_avx / merkletree_avx512 (poseidon_goldilocks.cpp:266-301, :484-520):
+ * tree = (2*nrows-1)*4 words, level-major, root last.  A row is ncols*dim words.  nrows must be a power of
+ * two (the reference reads a neighbour's node otherwise; every caller passes powers of two). */
+int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t dim);
+/* The level loop alone (poseidon_goldilocks.cpp:283-300): `level` holds n nodes (4 words each) followed by
+ * room for the n-1 nodes above them.  Used for the top log2(G) levels of the multi-GPU tree. */
+int glp_merkle_levels(glp_ctx *ctx, uint64_t *level, uint64_t n);
+/* MerklehashGoldilocks::getTreeNumElements (merklehash_goldilocks.hpp:24-27) */
+uint64_t glp_tree_num_elements(uint64_t nrows);
+/* MerkleTreeGL::getGroupProof (src/starkpil/merkleTree/merkleTreeGL.cpp:12-35): row idx of source followed by
+ * the sibling path; proof has width + 4*ceil(log2 height) words.  source / nodes may live on the device. */
+int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source, const uint64_t *nodes,
+                           uint64_t width, uint64_t height, uint64_t idx);
+
+/* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
+ * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip
+ * in between.  out_ext and tree may be NULL when the caller only needs the root (they are then kept in
+ * device scratch).  With host pointers the column blocks are streamed through pinned staging buffers. */
+int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
+               uint64_t n, uint64_t n_ext, uint64_t ncols);
+
+/* ---- synthetic data and checks used by bench.py / tests ---- */
+/* dst[i*ncols + c] = splitmix64(seed ^ ((row0+i)*ncols_total + col0 + c)) mod p, generated on the device */
+int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0,
+                   uint64_t ncols_total, uint64_t seed);
+/* out[0] = sum of all words mod p, out[1] = sum of word_i * (i+1) mod p  (order-sensitive checksum) */
+int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2]);
+/* exercises every device field primitive (PTX paths) on n pseudo-random + edge operands and returns the
+ * results for the host to compare against the oracle: out[5*i..] = add, sub, mul, mul_pow2(a, b%96), canon */
+int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t n, uint64_t *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

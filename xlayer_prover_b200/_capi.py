@@ -1,0 +1,239 @@
+"""ctypes binding of the C ABI declared in include/glprover.h.
+
+`load()` opens the in-tree libglprover.so (built by `python -m xlayer_prover_b200.build` / __graft_entry__.build()).
+There is no CPU implementation behind it: if the library is missing, or no CUDA device is usable,
+this raises -- it never falls back to anything.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_NAME = "libglprover.so"
+P = 0xFFFFFFFF00000001
+
+GLP_OK, GLP_E_ARG, GLP_E_DOMAIN, GLP_E_CUDA, GLP_E_OOM = 0, -1, -2, -3, -4
+
+u64, u32, i32, vp = C.c_uint64, C.c_uint32, C.c_int, C.c_void_p
+u64p = C.POINTER(C.c_uint64)
+
+# name -> (restype, argtypes); every symbol include/glprover.h declares
+SIGNATURES = {
+    "glp_init": (i32, [i32, C.POINTER(vp)]),
+    "glp_destroy": (None, [vp]),
+    "glp_last_error": (C.c_char_p, []),
+    "glp_set_stream": (i32, [vp, vp]),
+    "glp_synchronize": (i32, [vp]),
+    "glp_launch_count": (u64, [vp]),
+    "glp_set_scratch_limit": (i32, [vp, u64]),
+    "glp_device_alloc": (i32, [vp, u64, C.POINTER(vp)]),
+    "glp_device_free": (i32, [vp, vp]),
+    "glp_host_alloc": (i32, [vp, u64, C.POINTER(vp)]),
+    "glp_host_free": (i32, [vp, vp]),
+    "glp_memcpy": (i32, [vp, vp, vp, u64]),
+    "glp_mem_info": (i32, [vp, u64p, u64p]),
+    "glp_ntt": (i32, [vp, vp, vp, u64, u64, i32, i32]),
+    "glp_extend_pol": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_extend_pol_pitched": (i32, [vp, vp, u64, vp, u64, u64, u64, u64]),
+    "glp_reverse_permutation": (i32, [vp, vp, vp, u64, u64, u64, u64, u64]),
+    "glp_root": (u64, [u32, u64]),
+    "glp_hash_full_result": (i32, [vp, vp, vp, u64]),
+    "glp_linear_hash_rows": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_merkletree": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_merkle_levels": (i32, [vp, vp, u64]),
+    "glp_tree_num_elements": (u64, [u64]),
+    "glp_merkle_group_proof": (i32, [vp, vp, vp, vp, u64, u64, u64]),
+    "glp_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64]),
+    "glp_synth_fill": (i32, [vp, vp, u64, u64, u64, u64, u64, u64]),
+    "glp_checksum": (i32, [vp, vp, u64, u64p]),
+    "glp_field_selftest": (i32, [vp, vp, vp, u64, vp]),
+}
+
+
+class GlpError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("glprover error %d: %s" % (code, msg))
+        self.code = code
+
+
+class GlpLib:
+    """The shared library with typed entry points."""
+
+    def __init__(self, path):
+        if not os.path.exists(path):
+            raise FileNotFoundError(
+                "%s not found: build it with `python -m xlayer_prover_b200.build` "
+                "(nvcc, sm_100a).  There is no CPU fallback." % path)
+        self.path = path
+        self.cdll = C.CDLL(path)
+        for name, (res, args) in SIGNATURES.items():
+            f = getattr(self.cdll, name)      # AttributeError if the ABI and the library disagree
+            f.restype, f.argtypes = res, args
+            setattr(self, name, f)
+
+    def last_error(self):
+        return (self.glp_last_error() or b"").decode()
+
+    def check(self, rc):
+        if rc != GLP_OK:
+            raise GlpError(rc, self.last_error())
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is None:
+        _lib = GlpLib(os.path.join(HERE, LIB_NAME))
+    return _lib
+
+
+def ptr_of(a):
+    """Address of a numpy array, a torch tensor (host or CUDA), a raw int address, or None."""
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return a
+    if isinstance(a, np.ndarray):
+        if a.dtype != np.uint64 or not a.flags["C_CONTIGUOUS"]:
+            raise TypeError("expected a C-contiguous uint64 array")
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):            # torch.Tensor (int64 / uint64 storage, same bytes)
+        if a.element_size() != 8 or not a.is_contiguous():
+            raise TypeError("expected a contiguous 8-byte-element tensor")
+        return a.data_ptr()
+    raise TypeError("unsupported buffer type %r" % type(a))
+
+
+class Context:
+    """One glp_ctx: one device, one stream (include/glprover.h)."""
+
+    def __init__(self, device=0, lib=None):
+        self.lib = lib or load()
+        h = vp()
+        self.lib.check(self.lib.glp_init(device, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.glp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing
+    def set_stream(self, raw_stream): self.lib.check(self.lib.glp_set_stream(self.h, raw_stream))
+    def synchronize(self): self.lib.check(self.lib.glp_synchronize(self.h))
+    def launch_count(self): return self.lib.glp_launch_count(self.h)
+    def set_scratch_limit(self, nbytes): self.lib.check(self.lib.glp_set_scratch_limit(self.h, nbytes))
+
+    def device_alloc(self, nbytes):
+        p = vp()
+        self.lib.check(self.lib.glp_device_alloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def device_free(self, p): self.lib.check(self.lib.glp_device_free(self.h, p))
+
+    def host_alloc(self, nbytes):
+        p = vp()
+        self.lib.check(self.lib.glp_host_alloc(self.h, nbytes, C.byref(p)))
+        return p.value
+
+    def host_free(self, p): self.lib.check(self.lib.glp_host_free(self.h, p))
+    def memcpy(self, dst, src, nbytes): self.lib.check(self.lib.glp_memcpy(self.h, ptr_of(dst), ptr_of(src), nbytes))
+
+    def mem_info(self):
+        f, t = u64(), u64()
+        self.lib.check(self.lib.glp_mem_info(self.h, C.byref(f), C.byref(t)))
+        return f.value, t.value
+
+    def to_device(self, a):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        p = self.device_alloc(max(a.nbytes, 8))
+        self.memcpy(p, a, a.nbytes)
+        return p
+
+    def to_host(self, p, shape):
+        out = np.empty(shape, dtype=np.uint64)
+        self.memcpy(out, p, out.nbytes)
+        return out
+
+    # ---- the path
+    def ntt(self, dst, src, size, ncols=1, inverse=False, extend=False):
+        self.lib.check(self.lib.glp_ntt(self.h, ptr_of(dst), ptr_of(src), size, ncols, int(inverse), int(extend)))
+
+    def extend_pol(self, out, inp, n_ext, n, ncols):
+        self.lib.check(self.lib.glp_extend_pol(self.h, ptr_of(out), ptr_of(inp), n_ext, n, ncols))
+
+    def extend_pol_pitched(self, out, out_pitch, inp, in_pitch, n_ext, n, ncols):
+        self.lib.check(self.lib.glp_extend_pol_pitched(self.h, ptr_of(out), out_pitch, ptr_of(inp), in_pitch, n_ext, n, ncols))
+
+    def reverse_permutation(self, dst, src, size, offset_cols, ncols, ncols_all, extension=1):
+        self.lib.check(self.lib.glp_reverse_permutation(self.h, ptr_of(dst), ptr_of(src), size, offset_cols, ncols, ncols_all, extension))
+
+    def hash_full_result(self, out, inp, n=1):
+        self.lib.check(self.lib.glp_hash_full_result(self.h, ptr_of(out), ptr_of(inp), n))
+
+    def linear_hash_rows(self, out4, inp, ncols, pitch, nrows):
+        self.lib.check(self.lib.glp_linear_hash_rows(self.h, ptr_of(out4), ptr_of(inp), ncols, pitch, nrows))
+
+    def merkletree(self, tree, inp, ncols, nrows, dim=1):
+        self.lib.check(self.lib.glp_merkletree(self.h, ptr_of(tree), ptr_of(inp), ncols, nrows, dim))
+
+    def merkle_levels(self, level, n):
+        self.lib.check(self.lib.glp_merkle_levels(self.h, ptr_of(level), n))
+
+    def merkle_group_proof(self, proof, source, nodes, width, height, idx):
+        self.lib.check(self.lib.glp_merkle_group_proof(self.h, ptr_of(proof), ptr_of(source), ptr_of(nodes), width, height, idx))
+
+    def commit(self, out_ext, tree, inp, n, n_ext, ncols):
+        root = np.zeros(4, dtype=np.uint64)
+        self.lib.check(self.lib.glp_commit(self.h, ptr_of(out_ext), ptr_of(tree), ptr_of(root), ptr_of(inp), n, n_ext, ncols))
+        return root
+
+    def synth_fill(self, dst, nrows, ncols, seed, row0=0, col0=0, ncols_total=None):
+        self.lib.check(self.lib.glp_synth_fill(self.h, ptr_of(dst), nrows, ncols, row0, col0,
+                                                ncols if ncols_total is None else ncols_total, seed))
+
+    def checksum(self, src, nwords):
+        out = (u64 * 2)()
+        self.lib.check(self.lib.glp_checksum(self.h, ptr_of(src), nwords, out))
+        return int(out[0]), int(out[1])
+
+    def field_selftest(self, a, b):
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        b = np.ascontiguousarray(b, dtype=np.uint64)
+        out = np.zeros((a.size, 5), dtype=np.uint64)
+        self.lib.check(self.lib.glp_field_selftest(self.h, ptr_of(a), ptr_of(b), a.size, ptr_of(out)))
+        return out
+
+
+def tree_num_elements(nrows):
+    """MerklehashGoldilocks::getTreeNumElements (merklehash_goldilocks.hpp:24-27)."""
+    return (2 * nrows - 1) * 4 if nrows else 0
+
+
+def splitmix(seed, idx):
+    """Host twin of the device generator in csrc/aux_kernels.cuh (numpy, vectorised)."""
+    idx = np.asarray(idx, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        z = (np.uint64(seed) ^ idx) + np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+        return np.where(z >= np.uint64(P), z - np.uint64(P), z)
+
+
+def synth_matrix(nrows, ncols, seed, row0=0, col0=0, ncols_total=None):
+    nt = ncols if ncols_total is None else ncols_total
+    r = np.arange(row0, row0 + nrows, dtype=np.uint64)[:, None]
+    c = np.arange(col0, col0 + ncols, dtype=np.uint64)[None, :]
+    with np.errstate(over="ignore"):
+        return splitmix(seed, r * np.uint64(nt) + c)

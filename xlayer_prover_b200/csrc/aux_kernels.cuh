@@ -1,0 +1,92 @@
+// Small support kernels: synthetic trace generation, checksums, proof gather, field self-test.
+#pragma once
+#include "cuda_compat.h"
+#include "gl_field.cuh"
+
+// counter-based generator: v(i,c) = splitmix64(seed ^ (i*ncols_total + c)) mod p
+static __host__ __device__ __forceinline__ gl_t glp_splitmix(uint64_t seed, uint64_t idx)
+{
+    uint64_t z = (seed ^ idx) + 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    z ^= z >> 31;
+    return z >= GL_P ? z - GL_P : z;
+}
+
+__global__ void k_synth_fill(gl_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0, uint64_t ncols_total, uint64_t seed)
+{
+    const uint64_t total = nrows * ncols;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / ncols, c = i % ncols;
+        dst[i] = glp_splitmix(seed, (row0 + r) * ncols_total + col0 + c);
+    }
+}
+
+#define GLP_CK_THREADS 256
+// partial[2*block] = sum w_i, partial[2*block+1] = sum w_i*(i+1)   (mod p; exact, so order-independent)
+__global__ void __launch_bounds__(GLP_CK_THREADS)
+k_checksum(const gl_t *src, uint64_t n, gl_t *partial)
+{
+    __shared__ gl_t s0[GLP_CK_THREADS];
+    __shared__ gl_t s1[GLP_CK_THREADS];
+    gl_t a = 0, b = 0;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const gl_t w = src[i];
+        a = gl_add(a, w);
+        b = gl_add(b, gl_mul(w, (i + 1) % GL_P));
+    }
+    s0[threadIdx.x] = a;
+    s1[threadIdx.x] = b;
+    __syncthreads();
+    for (unsigned h = GLP_CK_THREADS / 2; h > 0; h >>= 1) {
+        if (threadIdx.x < h) {
+            s0[threadIdx.x] = gl_add(s0[threadIdx.x], s0[threadIdx.x + h]);
+            s1[threadIdx.x] = gl_add(s1[threadIdx.x], s1[threadIdx.x + h]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        partial[2 * blockIdx.x] = gl_canon(s0[0]);
+        partial[2 * blockIdx.x + 1] = gl_canon(s1[0]);
+    }
+}
+
+// MerkleTreeGL::getGroupProof (merkleTreeGL.cpp:12-35): row `idx` of source, then the sibling at every level
+__global__ void k_group_proof(gl_t *proof, const gl_t *source, const gl_t *nodes, uint64_t width, uint64_t height, uint64_t idx)
+{
+    for (uint64_t i = threadIdx.x; i < width; i += blockDim.x) proof[i] = gl_canon(source[idx * width + i]);
+    if (threadIdx.x < 4) {
+        uint64_t n = height, offset = 0, id = idx, lvl = 0;
+        while (n > 1) {
+            proof[width + 4 * lvl + threadIdx.x] = nodes[offset + (id ^ 1) * 4 + threadIdx.x];
+            offset += 4 * n;
+            n >>= 1;
+            id >>= 1;
+            lvl++;
+        }
+    }
+}
+
+// NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305), out of place
+__global__ void k_reverse_permutation(gl_t *dst, const gl_t *src, uint64_t size, uint32_t logn, uint64_t offset_cols, uint64_t ncols,
+                                      uint64_t ncols_all, uint64_t live)
+{
+    const uint64_t total = size * ncols;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / ncols, c = i % ncols;
+        const uint64_t br = logn ? (uint64_t)(__brev((unsigned)r) >> (32 - logn)) : 0;
+        dst[i] = br < live ? src[br * ncols_all + offset_cols + c] : 0;
+    }
+}
+
+__global__ void k_field_selftest(const gl_t *a, const gl_t *b, uint64_t n, gl_t *out)
+{
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const gl_t x = a[i], y = b[i];
+    out[5 * i + 0] = gl_canon(gl_add(x, y));
+    out[5 * i + 1] = gl_canon(gl_sub(x, y));
+    out[5 * i + 2] = gl_canon(gl_mul(x, y));
+    out[5 * i + 3] = gl_canon(gl_mul_pow2(x, (unsigned)(y % 96)));
+    out[5 * i + 4] = gl_canon(x);
+}

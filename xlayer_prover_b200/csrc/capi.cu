@@ -1,0 +1,827 @@
+// C ABI of libglprover.so (include/glprover.h): context, twiddle-table cache, pass planning, host<->device
+// staging, and the kernel launches for the NTT/LDE and Poseidon/Merkle paths.  No CPU implementation lives
+// here: every entry point ends in kernels from ntt_kernels.cuh / poseidon_kernels.cuh.
+#include "cuda_compat.h"
+#include "../../include/glprover.h"
+#include "poseidon_kernels.cuh"
+#include "ntt_kernels.cuh"
+#include "aux_kernels.cuh"
+
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <map>
+#include <string>
+#include <vector>
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CU(call)                                                                                           \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) return fail(GLP_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+#define GLP(call)                \
+    do {                         \
+        int rc_ = (call);        \
+        if (rc_ != GLP_OK) return rc_; \
+    } while (0)
+
+extern "C" const char *glp_last_error(void) { return g_err.c_str(); }
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+struct StepTab {
+    uint32_t nsteps = 0;
+    uint32_t step_log[NTT_MAX_STEPS] = {0, 0, 0, 0};
+    uint32_t ntw = 0;          // words
+    gl_t *tw = nullptr;        // device
+};
+struct TwoLevel {
+    gl_t *lo = nullptr, *hi = nullptr;
+};
+
+struct glp_ctx {
+    int device = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+    cudaStream_t copy_stream[2] = {nullptr, nullptr};
+    uint64_t launches = 0;
+    uint64_t scratch_limit = 0;
+    int ntt_cb = 4;
+    uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the 2/3-pass paths at small sizes
+    std::map<uint32_t, StepTab> step_tabs;   // by logQ
+    std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
+    std::map<uint32_t, TwoLevel> sc_tabs;    // shift^j / N, by logN
+    DevBuf s1, s2;                           // NTT scratch
+    DevBuf ext, nodes, tmp_in, tmp_out;      // commit / staging
+    DevBuf partial;                          // checksum partials
+    std::vector<void *> tables;              // everything to free
+};
+
+static int ensure(glp_ctx *ctx, DevBuf &b, size_t bytes)
+{
+    if (b.bytes >= bytes) return GLP_OK;
+    if (b.p) { cudaFree(b.p); b.p = nullptr; b.bytes = 0; }
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        char m[160];
+        snprintf(m, sizeof m, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+        return fail(GLP_E_OOM, m);
+    }
+    (void)ctx;
+    b.p = p;
+    b.bytes = bytes;
+    return GLP_OK;
+}
+static void release(DevBuf &b)
+{
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.bytes = 0;
+}
+
+#define LAUNCH(ctx, kernel, grid, block, smem, ...)                           \
+    do {                                                                      \
+        GLP_LAUNCH(kernel, grid, block, smem, (ctx)->stream, __VA_ARGS__);    \
+        (ctx)->launches++;                                                    \
+    } while (0)
+#define LAUNCH_FLAT(ctx, kernel, grid, block, ...)                            \
+    do {                                                                      \
+        GLP_LAUNCH_FLAT(kernel, grid, block, (ctx)->stream, __VA_ARGS__);     \
+        (ctx)->launches++;                                                    \
+    } while (0)
+
+extern "C" int glp_init(int device, glp_ctx **out)
+{
+    if (!out) return fail(GLP_E_ARG, "glp_init: ctx is NULL");
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return fail(GLP_E_CUDA, std::string("glp_init: no usable CUDA device (") + cudaGetErrorString(e) +
+                                    "); this library has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(GLP_E_ARG, "glp_init: device index out of range");
+    CU(cudaSetDevice(device));
+    glp_ctx *ctx = new glp_ctx();
+    ctx->device = device;
+    CU(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&ctx->copy_stream[0], cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&ctx->copy_stream[1], cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+    const char *cb = getenv("GLP_NTT_CB");
+    if (cb && (atoi(cb) == 2 || atoi(cb) == 4)) ctx->ntt_cb = atoi(cb);
+    const char *mq = getenv("GLP_NTT_MAX_LOGQ");
+    if (mq && atoi(mq) >= 1 && atoi(mq) <= NTT_MAX_LOGQ) ctx->max_logq = (uint32_t)atoi(mq);
+#ifndef GLP_EMU
+    CU(cudaFuncSetAttribute(k_ntt_tile<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    CU(cudaFuncSetAttribute(k_ntt_tile<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+#endif
+    *out = ctx;
+    return GLP_OK;
+}
+
+extern "C" void glp_destroy(glp_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (void *p : ctx->tables) cudaFree(p);
+    release(ctx->s1); release(ctx->s2); release(ctx->ext); release(ctx->nodes);
+    release(ctx->tmp_in); release(ctx->tmp_out); release(ctx->partial);
+    cudaStreamDestroy(ctx->own_stream);
+    cudaStreamDestroy(ctx->copy_stream[0]);
+    cudaStreamDestroy(ctx->copy_stream[1]);
+    delete ctx;
+}
+
+extern "C" int glp_set_stream(glp_ctx *ctx, void *s)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    ctx->stream = s ? (cudaStream_t)s : ctx->own_stream;
+    return GLP_OK;
+}
+extern "C" int glp_synchronize(glp_ctx *ctx)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+extern "C" uint64_t glp_launch_count(const glp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    ctx->scratch_limit = bytes;
+    return GLP_OK;
+}
+
+extern "C" int glp_device_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr)
+{
+    if (!ctx || !ptr) return fail(GLP_E_ARG, "glp_device_alloc: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    cudaError_t e = cudaMalloc(ptr, bytes ? bytes : 8);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(GLP_E_OOM, std::string("cudaMalloc: ") + cudaGetErrorString(e)); }
+    return GLP_OK;
+}
+extern "C" int glp_device_free(glp_ctx *ctx, void *ptr) { (void)ctx; if (ptr) CU(cudaFree(ptr)); return GLP_OK; }
+extern "C" int glp_host_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr)
+{
+    if (!ctx || !ptr) return fail(GLP_E_ARG, "glp_host_alloc: NULL argument");
+    cudaError_t e = cudaHostAlloc(ptr, bytes ? bytes : 8, cudaHostAllocDefault);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(GLP_E_OOM, std::string("cudaHostAlloc: ") + cudaGetErrorString(e)); }
+    return GLP_OK;
+}
+extern "C" int glp_host_free(glp_ctx *ctx, void *ptr) { (void)ctx; if (ptr) CU(cudaFreeHost(ptr)); return GLP_OK; }
+extern "C" int glp_memcpy(glp_ctx *ctx, void *dst, const void *src, uint64_t bytes)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!bytes) return GLP_OK;
+    CU(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+extern "C" int glp_mem_info(glp_ctx *ctx, uint64_t *free_bytes, uint64_t *total_bytes)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    size_t f = 0, t = 0;
+    CU(cudaMemGetInfo(&f, &t));
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return GLP_OK;
+}
+
+static bool on_device(const void *p)
+{
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+static uint32_t ilog2_u64(uint64_t n) { uint32_t r = 0; while (n > 1) { n >>= 1; r++; } return r; }
+static bool is_pow2(uint64_t n) { return n && !(n & (n - 1)); }
+
+// ------------------------------------------------------------------------------------------------
+// twiddle tables (K1)
+// ------------------------------------------------------------------------------------------------
+static gl_t host_root(uint32_t k) { return gl_canon(gl_root_of_unity(k)); }
+
+static int table_alloc(glp_ctx *ctx, size_t words, gl_t **out)
+{
+    void *p = nullptr;
+    cudaError_t e = cudaMalloc(&p, words * sizeof(gl_t));
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(GLP_E_OOM, "cudaMalloc(twiddle table) failed"); }
+    ctx->tables.push_back(p);
+    *out = (gl_t *)p;
+    return GLP_OK;
+}
+
+static int get_step_tab(glp_ctx *ctx, uint32_t logQ, const StepTab **out)
+{
+    auto it = ctx->step_tabs.find(logQ);
+    if (it != ctx->step_tabs.end()) { *out = &it->second; return GLP_OK; }
+    StepTab t;
+    uint32_t rem = logQ % 4, left = logQ;
+    if (rem) { t.step_log[t.nsteps++] = rem; left -= rem; }
+    while (left) { t.step_log[t.nsteps++] = 4; left -= 4; }
+    uint32_t lg = logQ;
+    for (uint32_t s = 0; s + 1 < t.nsteps; s++) { t.ntw += 1u << lg; lg -= t.step_log[s]; }
+    if (t.ntw) {
+        GLP(table_alloc(ctx, t.ntw, &t.tw));
+        gl_t *p = t.tw;
+        lg = logQ;
+        for (uint32_t s = 0; s + 1 < t.nsteps; s++) {
+            const uint32_t n = 1u << lg;
+            LAUNCH_FLAT(ctx, k_ntt_step_table, (n + 127) / 128, 128, p, lg, t.step_log[s]);
+            p += n;
+            lg -= t.step_log[s];
+        }
+        CU(cudaGetLastError());
+    }
+    ctx->step_tabs[logQ] = t;
+    *out = &ctx->step_tabs[logQ];
+    return GLP_OK;
+}
+
+// lo[e] = c * g^e (e < 2^min(logN,12)), hi[h] = g^(h << 12) (h < max(1, N >> 12))
+static int make_two_level(glp_ctx *ctx, uint32_t logN, gl_t c, gl_t g, TwoLevel *t)
+{
+    const uint64_t nlo = 1ull << (logN < NTT_LOGT ? logN : NTT_LOGT);
+    const uint64_t nhi = logN > NTT_LOGT ? (1ull << (logN - NTT_LOGT)) : 1;
+    GLP(table_alloc(ctx, nlo, &t->lo));
+    GLP(table_alloc(ctx, nhi, &t->hi));
+    LAUNCH_FLAT(ctx, k_ntt_pow_table, (unsigned)((nlo + 127) / 128), 128, t->lo, c, g, (uint64_t)1, nlo);
+    LAUNCH_FLAT(ctx, k_ntt_pow_table, (unsigned)((nhi + 127) / 128), 128, t->hi, (gl_t)1, g, (uint64_t)1 << NTT_LOGT, nhi);
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+static int get_tw_tab(glp_ctx *ctx, uint32_t logN, const TwoLevel **out)
+{
+    auto it = ctx->tw_tabs.find(logN);
+    if (it == ctx->tw_tabs.end()) {
+        TwoLevel t;
+        GLP(make_two_level(ctx, logN, 1, host_root(logN), &t));
+        it = ctx->tw_tabs.emplace(logN, t).first;
+    }
+    *out = &it->second;
+    return GLP_OK;
+}
+static int get_sc_tab(glp_ctx *ctx, uint32_t logN, const TwoLevel **out)
+{
+    auto it = ctx->sc_tabs.find(logN);
+    if (it == ctx->sc_tabs.end()) {
+        TwoLevel t;
+        const gl_t ninv = gl_canon(gl_inv((gl_t)((1ull << logN) % GL_P)));
+        GLP(make_two_level(ctx, logN, ninv, GL_SHIFT, &t));
+        it = ctx->sc_tabs.emplace(logN, t).first;
+    }
+    *out = &it->second;
+    return GLP_OK;
+}
+
+extern "C" uint64_t glp_root(uint32_t domain_pow, uint64_t idx)
+{
+    if (domain_pow > 32) return 0;
+    return gl_canon(gl_pow(host_root(domain_pow), idx));
+}
+
+// ------------------------------------------------------------------------------------------------
+// NTT passes (K2-K5)
+// ------------------------------------------------------------------------------------------------
+struct PassPlan {
+    uint32_t npass = 0;
+    uint32_t logq[3] = {0, 0, 0};
+};
+static PassPlan plan_passes(const glp_ctx *ctx, uint32_t logN)
+{
+    PassPlan p;
+    const uint32_t mq = ctx->max_logq;
+    if (logN <= mq) { p.npass = 1; p.logq[0] = logN; }
+    else if (logN <= 2 * mq) { p.npass = 2; p.logq[0] = (logN + 1) / 2; p.logq[1] = logN / 2; }
+    else { p.npass = 3; p.logq[0] = (logN + 2) / 3; p.logq[1] = (logN + 1) / 3; p.logq[2] = logN / 3; }
+    return p;
+}
+
+static size_t ntt_smem_bytes(uint32_t logQ, uint32_t ntw, int cb)
+{
+    const size_t Q = (size_t)1 << logQ;
+    return ((Q + (Q >> 4) + 1) * cb + ntw) * sizeof(gl_t);
+}
+
+// One transform of size 2^logN on `wb` columns: in (pitch/col0) -> out (pitch/col0), scratch holds 2^logN x wb.
+static int run_transform(glp_ctx *ctx, uint32_t logN, const gl_t *in, uint64_t in_pitch, uint64_t in_col0, gl_t *out,
+                         uint64_t out_pitch, uint64_t out_col0, uint32_t wb, uint64_t live, bool inverse, bool extend,
+                         gl_t *scratch)
+{
+    const PassPlan pl = plan_passes(ctx, logN);
+    const TwoLevel *tw = nullptr, *sc = nullptr;
+    if (pl.npass > 1) GLP(get_tw_tab(ctx, logN, &tw));
+    if (inverse && extend) GLP(get_sc_tab(ctx, logN, &sc));
+    uint32_t logL = logN;
+    for (uint32_t t = 0; t < pl.npass; t++) {
+        const bool first = (t == 0), last = (t + 1 == pl.npass);
+        const StepTab *st = nullptr;
+        GLP(get_step_tab(ctx, pl.logq[t], &st));
+        NttPass a;
+        memset(&a, 0, sizeof a);
+        a.in = first ? in : scratch;
+        a.in_pitch = first ? in_pitch : wb;
+        a.in_col0 = first ? in_col0 : 0;
+        a.out = last ? out : scratch;
+        a.out_pitch = last ? out_pitch : wb;
+        a.out_col0 = last ? out_col0 : 0;
+        a.live = first ? live : (1ull << logN);
+        a.wb = wb;
+        a.logN = logN;
+        a.logL = logL;
+        a.logQ = pl.logq[t];
+        a.last = last;
+        a.canon_in = first;
+        a.inverse = inverse;
+        a.extend = extend;
+        a.nprev = t;
+        a.logq_prev0 = pl.logq[0];
+        a.logq_prev1 = pl.logq[1];
+        a.nsteps = st->nsteps;
+        for (uint32_t s = 0; s < NTT_MAX_STEPS; s++) a.step_log[s] = st->step_log[s];
+        a.step_tw = st->tw;
+        a.tw_lo = tw ? tw->lo : nullptr;
+        a.tw_hi = tw ? tw->hi : nullptr;
+        a.sc_lo = sc ? sc->lo : nullptr;
+        a.sc_hi = sc ? sc->hi : nullptr;
+        a.ninv = gl_canon(gl_inv((gl_t)((1ull << logN) % GL_P)));
+        const uint64_t S = 1ull << (logL - a.logQ);
+        const int cb = ctx->ntt_cb;
+        const uint64_t nvg = (S * wb + cb - 1) / cb;
+        const uint64_t ntiles = (1ull << (logN - logL)) * nvg;
+        if (ntiles > 0x7FFFFFFFull) return fail(GLP_E_ARG, "NTT grid too large");
+        const size_t smem = ntt_smem_bytes(a.logQ, st->ntw, cb);
+        if (cb == 4) LAUNCH(ctx, k_ntt_tile<4>, (unsigned)ntiles, NTT_THREADS, smem, a);
+        else LAUNCH(ctx, k_ntt_tile<2>, (unsigned)ntiles, NTT_THREADS, smem, a);
+        logL -= a.logQ;
+    }
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+
+static uint64_t scratch_budget(glp_ctx *ctx)
+{
+    if (ctx->scratch_limit) return ctx->scratch_limit;
+    size_t f = 0, t = 0;
+    if (cudaMemGetInfo(&f, &t) != cudaSuccess) { cudaGetLastError(); f = (size_t)1 << 30; }
+    uint64_t b = (uint64_t)f / 4 + ctx->s1.bytes + ctx->s2.bytes;
+    const uint64_t cap = 16ull << 30;
+    return b > cap ? cap : b;
+}
+// columns per block so that `rows_total` scratch rows fit the budget
+static uint32_t pick_block_cols(glp_ctx *ctx, uint64_t rows_total, uint64_t ncols)
+{
+    uint64_t wb = scratch_budget(ctx) / (rows_total * sizeof(gl_t));
+    if (wb >= ncols) return (uint32_t)ncols;
+    if (wb >= 64) wb = 64 * (wb / 64);
+    else if (wb >= 8) wb = 8 * (wb / 8);
+    if (wb < 1) wb = 1;
+    return (uint32_t)wb;
+}
+
+// device pointers only
+static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src, uint64_t src_pitch, uint64_t size, uint64_t ncols,
+                   bool inverse, bool extend)
+{
+    const uint32_t logN = ilog2_u64(size);
+    const PassPlan pl = plan_passes(ctx, logN);
+    uint32_t wb = (uint32_t)ncols;
+    if (pl.npass > 1) {
+        wb = pick_block_cols(ctx, size, ncols);
+        GLP(ensure(ctx, ctx->s1, (size_t)size * wb * sizeof(gl_t)));
+    }
+    for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
+        const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+        GLP(run_transform(ctx, logN, src, src_pitch, c0, dst, dst_pitch, c0, w, size, inverse, extend, (gl_t *)ctx->s1.p));
+    }
+    return GLP_OK;
+}
+
+static int dev_extend_pol(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_t *in, uint64_t in_pitch, uint64_t n_ext, uint64_t n,
+                          uint64_t ncols)
+{
+    const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
+    const uint32_t wb = pick_block_cols(ctx, n_ext + n, ncols);
+    GLP(ensure(ctx, ctx->s1, (size_t)n_ext * wb * sizeof(gl_t)));
+    GLP(ensure(ctx, ctx->s2, (size_t)n * wb * sizeof(gl_t)));
+    gl_t *s1 = (gl_t *)ctx->s1.p, *s2 = (gl_t *)ctx->s2.p;
+    for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
+        const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+        // coefficients * shift^j / N  (INTT with extend, ntt_goldilocks.cpp:345)
+        GLP(run_transform(ctx, logN, in, in_pitch, c0, s2, w, 0, w, n, true, true, s1));
+        // zero-padded forward transform of size n_ext (ntt_goldilocks.cpp:346)
+        GLP(run_transform(ctx, logE, s2, w, 0, out, out_pitch, c0, w, n, false, false, s1));
+    }
+    return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host <-> device staging helpers
+// ------------------------------------------------------------------------------------------------
+// Bring a host matrix to a private device buffer (or pass a device pointer through).
+static int stage_in(glp_ctx *ctx, DevBuf &buf, const uint64_t *p, size_t words, const gl_t **dev)
+{
+    if (on_device(p)) { *dev = (const gl_t *)p; return GLP_OK; }
+    GLP(ensure(ctx, buf, words * sizeof(gl_t)));
+    CU(cudaMemcpyAsync(buf.p, p, words * sizeof(gl_t), cudaMemcpyHostToDevice, ctx->stream));
+    *dev = (const gl_t *)buf.p;
+    return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// NTT entry points
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (size == 0 || ncols == 0) return GLP_OK;                 // ntt_goldilocks.cpp:168-171
+    if (!src) return fail(GLP_E_ARG, "glp_ntt: src is NULL");
+    if (!is_pow2(size)) return fail(GLP_E_ARG, "glp_ntt: size is not a power of two");
+    if (size > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    if (ilog2_u64(size) > 3 * ctx->max_logq) return fail(GLP_E_ARG, "glp_ntt: size exceeds three tile passes");
+    if (!dst) dst = (uint64_t *)src;                            // ntt_goldilocks.cpp:15-22
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = (size_t)size * ncols;
+    const bool dst_dev = on_device(dst);
+    const gl_t *dsrc = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, src, words, &dsrc));
+    gl_t *ddst = (gl_t *)dst;
+    if (!dst_dev) {
+        // run in place on the staged copy when the source was staged, else into a private buffer
+        if ((const void *)dsrc == ctx->tmp_in.p) ddst = (gl_t *)ctx->tmp_in.p;
+        else { GLP(ensure(ctx, ctx->tmp_out, words * sizeof(gl_t))); ddst = (gl_t *)ctx->tmp_out.p; }
+    }
+    GLP(dev_ntt(ctx, ddst, ncols, dsrc, ncols, size, ncols, inverse != 0, inverse != 0 && extend != 0));
+    if (!dst_dev) CU(cudaMemcpyAsync(dst, ddst, words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_reverse_permutation(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t offset_cols,
+                                       uint64_t ncols, uint64_t ncols_all, uint64_t extension)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (size == 0 || ncols == 0) return GLP_OK;
+    if (!dst || !src) return fail(GLP_E_ARG, "glp_reverse_permutation: NULL pointer");
+    if (!is_pow2(size) || size > (1ull << 32)) return fail(GLP_E_ARG, "glp_reverse_permutation: size must be a power of two <= 2^32");
+    if (offset_cols + ncols > ncols_all) return fail(GLP_E_ARG, "glp_reverse_permutation: column window out of range");
+    if (dst == src && (extension > 1 || ncols != ncols_all || offset_cols != 0))
+        return fail(GLP_E_ARG, "glp_reverse_permutation: in place needs a single block and extension <= 1");   // :280-304
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t live = extension > 1 ? size / extension : size;
+    // only rows < live of src are ever read
+    const size_t src_words = (size_t)(live - 1) * ncols_all + offset_cols + ncols, dst_words = (size_t)size * ncols;
+    const gl_t *dsrc = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, src, src_words, &dsrc));
+    const bool dst_dev = on_device(dst);
+    gl_t *ddst = (gl_t *)dst;
+    if (!dst_dev || (const void *)ddst == (const void *)dsrc) { GLP(ensure(ctx, ctx->tmp_out, dst_words * sizeof(gl_t))); ddst = (gl_t *)ctx->tmp_out.p; }
+    const uint64_t nb = (dst_words + 255) / 256;
+    LAUNCH_FLAT(ctx, k_reverse_permutation, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, ddst, dsrc, size, ilog2_u64(size), offset_cols,
+                ncols, ncols_all, live);
+    CU(cudaGetLastError());
+    if ((void *)ddst != (void *)dst) CU(cudaMemcpyAsync(dst, ddst, dst_words * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+static int check_extend_args(const void *out, const void *in, uint64_t n_ext, uint64_t n)
+{
+    if (!in || !out) return fail(GLP_E_ARG, "extend_pol: NULL pointer");
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GLP_E_ARG, "extend_pol: sizes must be powers of two with n_ext >= n");
+    if (n_ext > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    return GLP_OK;
+}
+
+extern "C" int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_pitch, const uint64_t *in, uint64_t in_pitch,
+                                      uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n == 0 || ncols == 0) return GLP_OK;
+    GLP(check_extend_args(out, in, n_ext, n));
+    if (in_pitch < ncols || out_pitch < ncols) return fail(GLP_E_ARG, "extend_pol: pitch smaller than ncols");
+    CU(cudaSetDevice(ctx->device));
+    if (!on_device(in) || !on_device(out)) return fail(GLP_E_ARG, "glp_extend_pol_pitched: device pointers required");
+    GLP(dev_extend_pol(ctx, (gl_t *)out, out_pitch, (const gl_t *)in, in_pitch, n_ext, n, ncols));
+    return GLP_OK;
+}
+
+extern "C" int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n == 0 || ncols == 0) return GLP_OK;
+    GLP(check_extend_args(out, in, n_ext, n));
+    CU(cudaSetDevice(ctx->device));
+    const bool in_dev = on_device(in), out_dev = on_device(out);
+    if (in_dev && out_dev) {
+        GLP(dev_extend_pol(ctx, (gl_t *)out, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
+        CU(cudaStreamSynchronize(ctx->stream));
+        return GLP_OK;
+    }
+    return glp_commit(ctx, out, nullptr, nullptr, in, n, n_ext, ncols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Poseidon / Merkle
+// ------------------------------------------------------------------------------------------------
+extern "C" uint64_t glp_tree_num_elements(uint64_t nrows) { return nrows ? (2 * nrows - 1) * 4 : 0; }
+
+static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows)
+{
+    if (!nrows) return GLP_OK;
+    const int vec16 = (pitch % 2 == 0) && (((uintptr_t)in) % 16 == 0);
+    const uint64_t nblk = (nrows + POS_BLOCK - 1) / POS_BLOCK;
+    if (nblk > 0x7FFFFFFFull) return fail(GLP_E_ARG, "too many rows");
+    LAUNCH_FLAT(ctx, k_linear_hash_rows, (unsigned)nblk, POS_BLOCK, out4, in, ncols, pitch, nrows, vec16);
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+static int dev_tree_levels(glp_ctx *ctx, gl_t *level, uint64_t n)
+{
+    gl_t *cur = level;
+    while (n > 2 * POS_TOP_THREADS) {
+        gl_t *par = cur + 4 * n;
+        const uint64_t np = n / 2;
+        LAUNCH_FLAT(ctx, k_tree_level, (unsigned)((np + POS_BLOCK - 1) / POS_BLOCK), POS_BLOCK, par, (const gl_t *)cur, np);
+        cur = par;
+        n = np;
+    }
+    if (n > 1) LAUNCH(ctx, k_tree_top, 1, POS_TOP_THREADS, 0, cur, n);
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+static int dev_merkletree(glp_ctx *ctx, gl_t *tree, const gl_t *in, uint64_t width, uint64_t pitch, uint64_t nrows)
+{
+    GLP(dev_leaf_hash(ctx, tree, in, width, pitch, nrows));
+    GLP(dev_tree_levels(ctx, tree, nrows));
+    return GLP_OK;
+}
+
+extern "C" int glp_hash_full_result(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!n) return GLP_OK;
+    if (!out || !in) return fail(GLP_E_ARG, "glp_hash_full_result: NULL pointer");
+    CU(cudaSetDevice(ctx->device));
+    const gl_t *din = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, in, 12 * n, &din));
+    const bool out_dev = on_device(out);
+    gl_t *dout = (gl_t *)out;
+    if (!out_dev) { GLP(ensure(ctx, ctx->tmp_out, 12 * n * sizeof(gl_t))); dout = (gl_t *)ctx->tmp_out.p; }
+    LAUNCH_FLAT(ctx, k_permute_batch, (unsigned)((n + POS_BLOCK - 1) / POS_BLOCK), POS_BLOCK, dout, din, n);
+    CU(cudaGetLastError());
+    if (!out_dev) CU(cudaMemcpyAsync(out, dout, 12 * n * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_linear_hash_rows(glp_ctx *ctx, uint64_t *out4, const uint64_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!nrows) return GLP_OK;
+    if (!out4 || (!in && ncols)) return fail(GLP_E_ARG, "glp_linear_hash_rows: NULL pointer");
+    if (pitch < ncols) return fail(GLP_E_ARG, "glp_linear_hash_rows: pitch smaller than ncols");
+    CU(cudaSetDevice(ctx->device));
+    const gl_t *din = (const gl_t *)in;
+    if (ncols) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)(nrows - 1) * pitch + ncols, &din));
+    const bool out_dev = on_device(out4);
+    gl_t *dout = (gl_t *)out4;
+    if (!out_dev) { GLP(ensure(ctx, ctx->tmp_out, 4 * nrows * sizeof(gl_t))); dout = (gl_t *)ctx->tmp_out.p; }
+    GLP(dev_leaf_hash(ctx, dout, din, ncols, pitch, nrows));
+    if (!out_dev) CU(cudaMemcpyAsync(out4, dout, 4 * nrows * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t dim)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (nrows == 0) return GLP_OK;                                  // poseidon_goldilocks.cpp:268-271
+    const uint64_t width = ncols * dim;
+    if (!tree || (!in && width)) return fail(GLP_E_ARG, "glp_merkletree: NULL pointer");
+    if (!is_pow2(nrows)) return fail(GLP_E_ARG, "glp_merkletree: nrows must be a power of two");
+    CU(cudaSetDevice(ctx->device));
+    const size_t tw = glp_tree_num_elements(nrows);
+    const gl_t *din = (const gl_t *)in;
+    if (width) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)nrows * width, &din));
+    const bool out_dev = on_device(tree);
+    gl_t *dtree = (gl_t *)tree;
+    if (!out_dev) { GLP(ensure(ctx, ctx->nodes, tw * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+    GLP(dev_merkletree(ctx, dtree, din, width, width, nrows));
+    if (!out_dev) CU(cudaMemcpyAsync(tree, dtree, tw * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_merkle_levels(glp_ctx *ctx, uint64_t *level, uint64_t n)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n <= 1) return GLP_OK;
+    if (!level) return fail(GLP_E_ARG, "glp_merkle_levels: NULL pointer");
+    if (!is_pow2(n)) return fail(GLP_E_ARG, "glp_merkle_levels: n must be a power of two");
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = (size_t)(2 * n - 1) * 4;
+    const bool dev = on_device(level);
+    gl_t *d = (gl_t *)level;
+    if (!dev) {
+        GLP(ensure(ctx, ctx->nodes, words * sizeof(gl_t)));
+        d = (gl_t *)ctx->nodes.p;
+        CU(cudaMemcpyAsync(d, level, 4 * n * sizeof(gl_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    GLP(dev_tree_levels(ctx, d, n));
+    if (!dev) CU(cudaMemcpyAsync(level + 4 * n, d + 4 * n, (words - 4 * n) * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source, const uint64_t *nodes, uint64_t width,
+                                      uint64_t height, uint64_t idx)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!proof || !nodes || (!source && width)) return fail(GLP_E_ARG, "glp_merkle_group_proof: NULL pointer");
+    if (!is_pow2(height) || idx >= height) return fail(GLP_E_ARG, "glp_merkle_group_proof: bad height/idx");
+    const uint64_t depth = ilog2_u64(height);
+    const uint64_t words = width + 4 * depth;
+    if (!on_device(source) || !on_device(nodes)) {
+        // host-resident tree: this is a pure gather, do it where the data is (merkleTreeGL.cpp:12-35)
+        for (uint64_t i = 0; i < width; i++) proof[i] = gl_canon(source[idx * width + i]);
+        uint64_t n = height, off = 0, id = idx;
+        for (uint64_t l = 0; l < depth; l++) {
+            memcpy(proof + width + 4 * l, nodes + off + (id ^ 1) * 4, 4 * sizeof(uint64_t));
+            off += 4 * n; n >>= 1; id >>= 1;
+        }
+        return GLP_OK;
+    }
+    CU(cudaSetDevice(ctx->device));
+    GLP(ensure(ctx, ctx->tmp_out, words * sizeof(gl_t)));
+    LAUNCH(ctx, k_group_proof, 1, 128, 0, (gl_t *)ctx->tmp_out.p, (const gl_t *)source, (const gl_t *)nodes, width, height, idx);
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(proof, ctx->tmp_out.p, words * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// fused commit
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in, uint64_t n,
+                          uint64_t n_ext, uint64_t ncols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n == 0 || ncols == 0) return GLP_OK;
+    if (!in) return fail(GLP_E_ARG, "glp_commit: in is NULL");
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GLP_E_ARG, "glp_commit: sizes must be powers of two with n_ext >= n");
+    if (n_ext > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    CU(cudaSetDevice(ctx->device));
+    const bool want_tree = tree != nullptr || root != nullptr;
+    const size_t in_words = (size_t)n * ncols, ext_words = (size_t)n_ext * ncols, tree_words = glp_tree_num_elements(n_ext);
+    const bool in_dev = on_device(in), ext_dev = on_device(out_ext), tree_dev = on_device(tree);
+
+    // extended matrix lives on the device for the Merkle stage whatever the caller's pointers are
+    gl_t *dext = (gl_t *)out_ext;
+    if (!ext_dev) { GLP(ensure(ctx, ctx->ext, ext_words * sizeof(gl_t))); dext = (gl_t *)ctx->ext.p; }
+    gl_t *dtree = (gl_t *)tree;
+    if (want_tree && !tree_dev) { GLP(ensure(ctx, ctx->nodes, tree_words * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+
+    if (in_dev) {
+        GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
+        if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+        // Host input: stream column blocks.  Block k+1 is uploaded (strided 2-D copy out of the row-major host
+        // matrix) on a copy stream while block k is transformed, and finished blocks of the extension are
+        // downloaded on the other copy stream while later blocks are still being computed.
+        const uint32_t wb = pick_block_cols(ctx, 2 * (n_ext + n), ncols);   // scratch + double-buffered upload
+        GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * wb * sizeof(gl_t)));
+        gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * wb};
+        const uint64_t nblocks = (ncols + wb - 1) / wb;
+        std::vector<cudaEvent_t> up(nblocks), done(nblocks), free_stage(nblocks);
+        for (uint64_t k = 0; k < nblocks; k++) {
+            CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&free_stage[k], cudaEventDisableTiming));
+        }
+        auto upload = [&](uint64_t k) -> int {
+            const uint64_t c0 = k * wb;
+            const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+            if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], free_stage[k - 2], 0));
+            CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)w * 8, in + c0, (size_t)ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice,
+                                 ctx->copy_stream[0]));
+            CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
+            return GLP_OK;
+        };
+        GLP(upload(0));
+        for (uint64_t k = 0; k < nblocks; k++) {
+            const uint64_t c0 = k * wb;
+            const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+            if (k + 1 < nblocks) GLP(upload(k + 1));
+            CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
+            GLP(ensure(ctx, ctx->s1, (size_t)n_ext * wb * sizeof(gl_t)));
+            GLP(ensure(ctx, ctx->s2, (size_t)n * wb * sizeof(gl_t)));
+            const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
+            GLP(run_transform(ctx, logN, stage[k & 1], w, 0, (gl_t *)ctx->s2.p, w, 0, w, n, true, true, (gl_t *)ctx->s1.p));
+            CU(cudaEventRecord(free_stage[k], ctx->stream));
+            GLP(run_transform(ctx, logE, (gl_t *)ctx->s2.p, w, 0, dext, ncols, c0, w, n, false, false, (gl_t *)ctx->s1.p));
+            CU(cudaEventRecord(done[k], ctx->stream));
+            if (out_ext && !ext_dev) {
+                CU(cudaStreamWaitEvent(ctx->copy_stream[1], done[k], 0));
+                CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)ncols * 8, dext + c0, (size_t)ncols * 8, (size_t)w * 8, n_ext,
+                                     cudaMemcpyDeviceToHost, ctx->copy_stream[1]));
+            }
+        }
+        for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(free_stage[k]); }
+        // `done` events are destroyed after the final sync below
+        if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+        if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaStreamSynchronize(ctx->copy_stream[0]));
+        CU(cudaStreamSynchronize(ctx->copy_stream[1]));
+        for (uint64_t k = 0; k < nblocks; k++) cudaEventDestroy(done[k]);
+        (void)in_words;
+        return GLP_OK;
+    }
+    if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+    if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// synthetic data, checksums, self-test
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0,
+                              uint64_t ncols_total, uint64_t seed)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!nrows || !ncols) return GLP_OK;
+    if (!dst) return fail(GLP_E_ARG, "glp_synth_fill: dst is NULL");
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = (size_t)nrows * ncols;
+    const bool dev = on_device(dst);
+    gl_t *d = (gl_t *)dst;
+    if (!dev) { GLP(ensure(ctx, ctx->tmp_out, words * sizeof(gl_t))); d = (gl_t *)ctx->tmp_out.p; }
+    const uint64_t nb = (words + 255) / 256;
+    LAUNCH_FLAT(ctx, k_synth_fill, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, d, nrows, ncols, row0, col0, ncols_total, seed);
+    CU(cudaGetLastError());
+    if (!dev) { CU(cudaMemcpyAsync(dst, d, words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream)); CU(cudaStreamSynchronize(ctx->stream)); }
+    return GLP_OK;
+}
+
+extern "C" int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2])
+{
+    if (!ctx || !out) return fail(GLP_E_ARG, "glp_checksum: NULL argument");
+    out[0] = out[1] = 0;
+    if (!n) return GLP_OK;
+    if (!on_device(src)) return fail(GLP_E_ARG, "glp_checksum: device pointer required");
+    CU(cudaSetDevice(ctx->device));
+    const unsigned nb = 148 * 8;
+    GLP(ensure(ctx, ctx->partial, 2 * nb * sizeof(gl_t)));
+    LAUNCH(ctx, k_checksum, nb, GLP_CK_THREADS, 0, (const gl_t *)src, n, (gl_t *)ctx->partial.p);
+    CU(cudaGetLastError());
+    std::vector<gl_t> h(2 * nb);
+    CU(cudaMemcpyAsync(h.data(), ctx->partial.p, 2 * nb * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    gl_t a = 0, b = 0;
+    for (unsigned i = 0; i < nb; i++) { a = gl_add(a, h[2 * i]); b = gl_add(b, h[2 * i + 1]); }
+    out[0] = gl_canon(a);
+    out[1] = gl_canon(b);
+    return GLP_OK;
+}
+
+extern "C" int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t n, uint64_t *out)
+{
+    if (!ctx || !a || !b || !out) return fail(GLP_E_ARG, "glp_field_selftest: NULL argument");
+    if (!n) return GLP_OK;
+    CU(cudaSetDevice(ctx->device));
+    DevBuf da, db, dout;
+    int rc = ensure(ctx, da, n * 8);
+    if (rc == GLP_OK) rc = ensure(ctx, db, n * 8);
+    if (rc == GLP_OK) rc = ensure(ctx, dout, 5 * n * 8);
+    if (rc == GLP_OK) {
+        cudaMemcpyAsync(da.p, a, n * 8, cudaMemcpyDefault, ctx->stream);
+        cudaMemcpyAsync(db.p, b, n * 8, cudaMemcpyDefault, ctx->stream);
+        LAUNCH_FLAT(ctx, k_field_selftest, (unsigned)((n + 127) / 128), 128, (const gl_t *)da.p, (const gl_t *)db.p, n, (gl_t *)dout.p);
+        cudaMemcpyAsync(out, dout.p, 5 * n * 8, cudaMemcpyDefault, ctx->stream);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) rc = fail(GLP_E_CUDA, cudaGetErrorString(e));
+    }
+    release(da); release(db); release(dout);
+    return rc;
+}

@@ -1,0 +1,240 @@
+// K0 -- Goldilocks field F_p, p = 2^64 - 2^32 + 1, device arithmetic for sm_100a.
+//
+// Replaces the reference's scalar field ops (src/goldilocks/src/goldilocks_base_field_scalar.hpp:16-35 add,
+// :62-80 sub, :103-160 mul; constants goldilocks_base_field.cpp:5-51).  Same contract as the reference:
+// operands and results are raw uint64_t in [0, 2^64) -- NOT necessarily canonical -- and every
+// function accepts non-canonical inputs.  gl_canon() is the reference's Goldilocks::toU64
+// (goldilocks_base_field_tools.hpp:146-163); every kernel applies it once on the way out, so everything
+// this library emits is canonical.
+//
+// The identities used:  2^64 = 2^32 - 1 =: EPS (mod p),  2^96 = -1 (mod p).
+// A 64x64 product is four IMAD.WIDE.U32 (32-bit limbs); the 128-bit result p3:p2:p1:p0 folds as
+//     (p1:p0) - p3 + p2*EPS      with one conditional -EPS (borrow) and one conditional +EPS (carry).
+// The PTX below pins the carry chains so ptxas emits 4 IMAD.WIDE + 14 integer ops per multiply
+// (the plain C++ form compiles to 29).  The portable branch is the same arithmetic in C++ and is what
+// the host-thread emulator (tests/cuemu) runs.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDA_ARCH__)
+#define GL_DEVICE_PTX 1
+#else
+#define GL_DEVICE_PTX 0
+#endif
+
+#ifndef GL_HD
+#if defined(__CUDACC__)
+#define GL_HD __host__ __device__ __forceinline__
+#else
+#define GL_HD static inline
+#endif
+#endif
+
+typedef unsigned long long gl_t;   // same width as the reference's Goldilocks::Element::fe (uint64_t)
+
+#define GL_P 0xFFFFFFFF00000001ULL
+#define GL_EPS 0xFFFFFFFFULL
+// generator of the 2^32 roots of unity: the reference's Goldilocks::W[32] (goldilocks_base_field.cpp:44);
+// W[k] = GL_W32^(2^(32-k)), which makes W[6] = 8: every 64th root of unity is a power of two.
+#define GL_W32 7277203076849721926ULL
+#define GL_SHIFT 7ULL              // coset generator, Goldilocks::SHIFT (goldilocks_base_field.cpp:50)
+
+GL_HD gl_t gl_canon(gl_t a) { return a >= GL_P ? a - GL_P : a; }
+
+// a + b (mod p).  Handles the double wrap the reference handles (two non-canonical operands).
+GL_HD gl_t gl_add(gl_t a, gl_t b)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,m;\n\t"
+        "mov.b64 {a0,a1}, %1;\n\t"
+        "mov.b64 {b0,b1}, %2;\n\t"
+        "add.cc.u32 a0, a0, b0;\n\t"
+        "addc.cc.u32 a1, a1, b1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"                 // carry
+        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"   // + carry*EPS
+        "madc.hi.cc.u32 a1, m, 0xffffffff, a1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"                 // second wrap (only when both operands >= p-ish)
+        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"
+        "madc.hi.u32 a1, m, 0xffffffff, a1;\n\t"
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+#else
+    gl_t r = a + b;
+    if (r < a) { gl_t r2 = r + GL_EPS; if (r2 < r) r2 += GL_EPS; r = r2; }
+    return r;
+#endif
+}
+
+// a + b where at least one operand is canonical (< p): a single wrap suffices.
+GL_HD gl_t gl_add_c(gl_t a, gl_t b)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,m;\n\t"
+        "mov.b64 {a0,a1}, %1;\n\t"
+        "mov.b64 {b0,b1}, %2;\n\t"
+        "add.cc.u32 a0, a0, b0;\n\t"
+        "addc.cc.u32 a1, a1, b1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"
+        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"
+        "madc.hi.u32 a1, m, 0xffffffff, a1;\n\t"
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+#else
+    gl_t r = a + b;
+    if (r < a) r += GL_EPS;
+    return r;
+#endif
+}
+
+// a - b (mod p)
+GL_HD gl_t gl_sub(gl_t a, gl_t b)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,m;\n\t"
+        "mov.b64 {a0,a1}, %1;\n\t"
+        "mov.b64 {b0,b1}, %2;\n\t"
+        "sub.cc.u32 a0, a0, b0;\n\t"
+        "subc.cc.u32 a1, a1, b1;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                 // 0xffffffff on borrow
+        "sub.cc.u32 a0, a0, m;\n\t"             // - EPS on borrow
+        "subc.cc.u32 a1, a1, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                 // second wrap
+        "sub.cc.u32 a0, a0, m;\n\t"
+        "subc.u32 a1, a1, 0;\n\t"
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+#else
+    gl_t r = a - b;
+    if (a < b) { gl_t r2 = r - GL_EPS; if (r2 > r) r2 -= GL_EPS; r = r2; }
+    return r;
+#endif
+}
+
+GL_HD gl_t gl_neg(gl_t a) { return gl_sub(0, a); }
+
+// fold a 128-bit value hi:lo to 64 bits (mod p)
+GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 p0,p1,p2,p3,m;\n\t"
+        "mov.b64 {p0,p1}, %1;\n\t"
+        "mov.b64 {p2,p3}, %2;\n\t"
+        "sub.cc.u32 p0, p0, p3;\n\t"            // (p1:p0) - p3          [2^96 = -1]
+        "subc.cc.u32 p1, p1, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 p0, p0, m;\n\t"             //   - EPS on borrow
+        "subc.u32 p1, p1, 0;\n\t"
+        "mad.lo.cc.u32 p0, p2, 0xffffffff, p0;\n\t"  // + p2*EPS        [2^64 = EPS]
+        "madc.hi.cc.u32 p1, p2, 0xffffffff, p1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"
+        "mad.lo.cc.u32 p0, m, 0xffffffff, p0;\n\t"   //   + EPS on carry
+        "madc.hi.u32 p1, m, 0xffffffff, p1;\n\t"
+        "mov.b64 %0, {p0,p1};\n\t"
+        "}" : "=l"(r) : "l"(lo), "l"(hi));
+    return r;
+#else
+    uint32_t h0 = (uint32_t)hi, h1 = (uint32_t)(hi >> 32);
+    gl_t t = lo - h1;
+    if (lo < h1) t -= GL_EPS;
+    gl_t u = ((gl_t)h0 << 32) - h0;
+    gl_t r = t + u;
+    if (r < u) r += GL_EPS;
+    return r;
+#endif
+}
+
+// full 64x64 -> 128 product as 32-bit limbs (4 IMAD.WIDE.U32)
+GL_HD void gl_mul_wide(gl_t a, gl_t b, gl_t &lo, gl_t &hi)
+{
+#if GL_DEVICE_PTX
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,x0,x1,s0,s1,s2,y0,y1,z0,z1;\n\t"
+        ".reg .u64 X,Y,Z;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "mul.wide.u32 Z, a0, b0;\n\t"
+        "mul.wide.u32 X, a0, b1;\n\t"
+        "mul.wide.u32 Y, a1, b1;\n\t"
+        "mov.b64 {x0,x1}, X;\n\t"
+        "mad.lo.cc.u32 s0, a1, b0, x0;\n\t"
+        "madc.hi.cc.u32 s1, a1, b0, x1;\n\t"
+        "addc.u32 s2, 0, 0;\n\t"
+        "mov.b64 {z0,z1}, Z;\n\t"
+        "mov.b64 {y0,y1}, Y;\n\t"
+        "add.cc.u32 z1, z1, s0;\n\t"
+        "addc.cc.u32 y0, y0, s1;\n\t"
+        "addc.u32 y1, y1, s2;\n\t"
+        "mov.b64 %0, {z0,z1};\n\t"
+        "mov.b64 %1, {y0,y1};\n\t"
+        "}" : "=l"(lo), "=l"(hi) : "l"(a), "l"(b));
+#else
+    unsigned __int128 w = (unsigned __int128)a * b;
+    lo = (gl_t)w;
+    hi = (gl_t)(w >> 64);
+#endif
+}
+
+GL_HD gl_t gl_mul(gl_t a, gl_t b)
+{
+    gl_t lo, hi;
+    gl_mul_wide(a, b, lo, hi);
+    return gl_reduce128(lo, hi);
+}
+
+GL_HD gl_t gl_sqr(gl_t a) { return gl_mul(a, a); }
+
+// x^7, the Poseidon S-box (poseidon_goldilocks.hpp:91-97): 4 multiplies
+GL_HD gl_t gl_pow7(gl_t x)
+{
+    gl_t x2 = gl_mul(x, x);
+    gl_t x3 = gl_mul(x, x2);
+    gl_t x4 = gl_mul(x2, x2);
+    return gl_mul(x3, x4);
+}
+
+GL_HD gl_t gl_pow(gl_t b, uint64_t e)
+{
+    gl_t r = 1;
+    while (e) {
+        if (e & 1) r = gl_mul(r, b);
+        b = gl_mul(b, b);
+        e >>= 1;
+    }
+    return r;
+}
+
+GL_HD gl_t gl_inv(gl_t a) { return gl_pow(a, GL_P - 2); }
+
+// a * 2^k (mod p) for 0 <= k < 96: shifts and one fold, no multiplier.  Because W[6] = 8 every twiddle
+// of a 64-point (and so of a 16-point) transform is such a power of two.
+GL_HD gl_t gl_mul_pow2(gl_t a, unsigned k)
+{
+    // a * 2^k = v0 + v1*2^64 + v2*2^128 with v2*2^128 = v2 * 2^96 * 2^32 = -(v2 << 32)
+    gl_t v0, v1, v2;
+    if (k == 0) return a;
+    if (k < 64) { v0 = a << k; v1 = a >> (64 - k); v2 = 0; }
+    else if (k == 64) { v0 = 0; v1 = a; v2 = 0; }
+    else { v0 = 0; v1 = a << (k - 64); v2 = a >> (128 - k); }
+    gl_t r = gl_reduce128(v0, v1);
+    if (k > 64) r = gl_sub(r, v2 << 32);     // v2 < 2^32
+    return r;
+}
+
+// primitive 2^k-th root of unity, the reference's Goldilocks::w(k)
+GL_HD gl_t gl_root_of_unity(unsigned k)
+{
+    gl_t w = GL_W32;
+    for (unsigned i = k; i < 32; i++) w = gl_mul(w, w);
+    return w;
+}

@@ -1,0 +1,121 @@
+// K6 (leaf hash), K7 (tree levels) and the batched bare permutation.
+//
+//  k_linear_hash_rows : one thread = one leaf row; the reference's PoseidonGoldilocks::linear_hash
+//                       (poseidon_goldilocks.cpp:229-265) for every row of a row-major matrix.
+//  k_tree_level       : one thread = one parent node; one level of the loop in merkletree_avx
+//                       (poseidon_goldilocks.cpp:283-300).
+//  k_tree_top         : a single CTA finishes the last levels (<= 2*TOP_THREADS nodes) without relaunching.
+//  k_permute_batch    : hash_full_result (poseidon_goldilocks.cpp:166-228) on n independent 12-word states.
+//
+// Roofline: integer issue.  A leaf row of C columns costs ceil(C/8) permutations (~2.2e4 integer
+// instructions each) against 8*C bytes of HBM traffic, i.e. > 300 instructions per byte: the row loads are
+// software-prefetched one sponge block ahead and otherwise left to the L1/L2 (each thread streams its own
+// 64-byte-aligned chunks, so every 32-byte sector fetched is fully used).
+#pragma once
+#include "cuda_compat.h"
+#include "poseidon.cuh"
+
+#define POS_BLOCK 128
+
+// load 8 consecutive words of a row (zero beyond `n` words)
+static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restrict__ p, uint32_t n, bool vec16)
+{
+#if !defined(GLP_EMU)
+    if (vec16 && n >= 8) {
+        const ulonglong2 *q = reinterpret_cast<const ulonglong2 *>(p);
+#pragma unroll
+        for (int i = 0; i < 4; i++) { ulonglong2 t = __ldg(q + i); v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+        return;
+    }
+#else
+    (void)vec16;
+#endif
+#pragma unroll
+    for (int i = 0; i < 8; i++) v[i] = (uint32_t)i < n ? __ldg(p + i) : 0;
+}
+
+// out[row*4 .. +4) = linear_hash(in[row*pitch .. +ncols))
+__global__ void __launch_bounds__(POS_BLOCK)
+k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16)
+{
+    uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= nrows) return;
+    const gl_t *p = in + row * pitch;
+    gl_t *o = out + row * 4;
+    if (ncols <= POS_CAP) {                       // size <= CAPACITY: copy and zero-pad, no hashing (:234-239)
+#pragma unroll
+        for (int i = 0; i < 4; i++) o[i] = (uint64_t)i < ncols ? gl_canon(p[i]) : 0;
+        return;
+    }
+    gl_t x[12];
+    gl_t nxt[8];
+    uint64_t nblk = (ncols + 7) / 8;
+    pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16 != 0);
+#pragma unroll
+    for (int i = 8; i < 12; i++) x[i] = 0;        // capacity starts at zero (:243-246)
+#pragma unroll 1
+    for (uint64_t b = 0; b < nblk; b++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) x[i] = nxt[i];
+        if (b + 1 < nblk) {                        // prefetch the next 64 bytes of this row under the permutation
+            uint64_t rem = ncols - 8 * (b + 1);
+            pos_load8(nxt, p + 8 * (b + 1), (uint32_t)(rem < 8 ? rem : 8), vec16 != 0);
+        }
+        pos_permute(x);
+#pragma unroll
+        for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
+}
+
+// parents[i] = H(children[2i] || children[2i+1] || 0000)[0:4]
+static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src)
+{
+    gl_t x[12];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = src[i];
+#pragma unroll
+    for (int i = 8; i < 12; i++) x[i] = 0;
+    pos_permute(x);
+#pragma unroll
+    for (int i = 0; i < 4; i++) dst[i] = gl_canon(x[i]);
+}
+
+__global__ void __launch_bounds__(POS_BLOCK)
+k_tree_level(gl_t *__restrict__ parents, const gl_t *__restrict__ children, uint64_t nparents)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nparents) return;
+    pos_hash_pair(parents + 4 * i, children + 8 * i);
+}
+
+// One CTA walks the remaining levels: `level` holds n nodes (n a power of two, n <= 2*blockDim.x) followed
+// in memory by its parents, their parents, ... (the reference's level-major layout).
+#define POS_TOP_THREADS 128
+__global__ void __launch_bounds__(POS_TOP_THREADS)
+k_tree_top(gl_t *level, uint64_t n)
+{
+    gl_t *cur = level;
+    while (n > 1) {
+        uint64_t np = n >> 1;
+        gl_t *par = cur + 4 * n;
+        if (threadIdx.x < np) pos_hash_pair(par + 4 * threadIdx.x, cur + 8 * threadIdx.x);
+        __syncthreads();
+        cur = par;
+        n = np;
+    }
+}
+
+__global__ void __launch_bounds__(POS_BLOCK)
+k_permute_batch(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t n)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    gl_t x[12];
+#pragma unroll
+    for (int k = 0; k < 12; k++) x[k] = in[12 * i + k];
+    pos_permute(x);
+#pragma unroll
+    for (int k = 0; k < 12; k++) out[12 * i + k] = gl_canon(x[k]);
+}
