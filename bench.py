@@ -1,0 +1,484 @@
+#!/usr/bin/env python3
+"""bench.py -- the STARK-commitment hot path on B200: LDE (extendPol) + Poseidon Merkle commit.
+
+    python bench.py --gpus 1 --steps K --warmup W                 (one GPU)
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+           bench.py --gpus N --steps K --warmup W                  (N GPUs, one rank each, NCCL)
+    python bench.py --impl reference ...                           (the reference's own CPU code, host cores)
+
+Workload (BASELINE.json configs[1]): synthetic 2^23 rows x 660 committed columns, blowup 2 -> 2^24 rows,
+extendPol + MerkleTreeGL root.  A "step" is one full commit of that matrix.  The metric is throughput, so
+that the CPU arms -- which run a bounded column sample of the same workload -- are directly comparable:
+    value [Melem/s] = 10^-6 * (N rows * C columns committed) / seconds per commit      (higher is better)
+`commit_ms` and `poseidon_hash_per_s` (BASELINE.json's two raw figures) ride along in the same JSON line.
+
+  value : inputs already resident in HBM, CUDA events on the launching stream, max over ranks.
+  e2e   : the same commit through the C ABI with HOST (pinned) buffers: H2D of the trace and D2H of the
+          extended matrix + every Merkle node inside the timed region.
+  N > 1 : column-sharded LDE -> one NCCL all-to-all -> row-sharded subtrees -> top levels on rank 0
+          (xlayer_prover_b200/sharded.py); total work is fixed, so "scaling": "strong".
+Only the cpu_baseline leg and --impl reference execute anything under oracle/ (as the thing measured there);
+the parity spot-check after the timed region uses it as the checker.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+P = 0xFFFFFFFF00000001
+SEED = 0x9E3779B97F4A7C15 + 2          # seed = golden ratio + config id
+SASS_INSTR_PER_PERM = 24143            # tools/sass_count.py on k_permute_batch (profiles/r01_sass_counts.txt)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--log-rows", type=int, default=23)
+    ap.add_argument("--cols", type=int, default=660)
+    ap.add_argument("--log-blowup", type=int, default=1)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="target seconds of CPU work for the cpu_baseline sample")
+    return ap.parse_args()
+
+
+def perms_per_commit(n_ext, ncols):
+    return n_ext * ((ncols + 7) // 8) + n_ext - 1 if ncols > 4 else n_ext - 1
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# --------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU arms (the reference's own code on the host cores)
+# --------------------------------------------------------------------------------------------
+def cpu_oracle():
+    from oracle import refbind
+    ref = refbind.reference()
+    if ref is not None:
+        return ref, "reference"
+    subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "port"], check=True, capture_output=True)
+    return refbind.port(), "port"
+
+
+def cpu_sample_cols(orc, log_rows, log_blowup, ncols, budget_s, nsteps):
+    """Pick the column count of the bounded CPU sample: calibrate on 2^16 rows, predict 2^log_rows."""
+    from xlayer_prover_b200._capi import synth_matrix
+    n0 = 1 << 16
+    a = synth_matrix(n0, 16, SEED)
+    orc.commit(a, n0 << log_blowup)                                   # warm caches / thread pool
+    _, _, (t_lde, t_mt) = orc.commit(a, n0 << log_blowup)
+    n = 1 << log_rows
+    scale = (n / n0)
+    lde_per_col = t_lde / 16 * scale * (log_rows + 1.0) / 17.0        # ~ N log N
+    perm_s = t_mt / perms_per_commit(n0 << log_blowup, 16)
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 32 << 30
+    best = 8
+    for c in (8, 16, 32, 64, 128, 256, 512):
+        if c > ncols:
+            break
+        est = lde_per_col * c + perm_s * perms_per_commit(n << log_blowup, c)
+        mem = 8 * n * c * (1 + 2 * (1 << log_blowup)) + 32 * (2 * (n << log_blowup))
+        if est * nsteps <= budget_s and mem <= 0.5 * avail:
+            best = c
+    return best
+
+
+def cpu_commit_step(orc, a, n_ext):
+    t0 = time.perf_counter()
+    _, tree, (t_lde, t_mt) = orc.commit(a, n_ext)
+    return time.perf_counter() - t0, t_lde, t_mt, tree
+
+
+def run_cpu_baseline(args, budget_s, nsteps=1, warmup=0):
+    """Times the oracle (oracle/_ref when the reference compiled, else the C port) on 2^log_rows rows x C' columns."""
+    from xlayer_prover_b200._capi import synth_matrix
+    orc, kind = cpu_oracle()
+    cores = orc.max_threads()
+    n, n_ext = 1 << args.log_rows, 1 << (args.log_rows + args.log_blowup)
+    c = cpu_sample_cols(orc, args.log_rows, args.log_blowup, args.cols, budget_s, nsteps + warmup)
+    a = synth_matrix(n, c, SEED, ncols_total=args.cols)
+    for _ in range(warmup):
+        cpu_commit_step(orc, a, n_ext)
+    times, lde, mt = [], [], []
+    for _ in range(nsteps):
+        t, tl, tm, _ = cpu_commit_step(orc, a, n_ext)
+        times.append(t)
+        lde.append(tl)
+        mt.append(tm)
+    t = (sum(lde) + sum(mt)) / len(times)        # the reference's own two calls; numpy buffer allocation excluded
+    return {
+        "value": n * c / t / 1e6, "unit": "Melem/s", "cores": cores, "kind": kind,
+        "sample": "2^%d rows x %d of %d columns, blowup %d, %d timed step(s); extendPol %.2f s + merkletree %.2f s per step"
+                  % (args.log_rows, c, args.cols, 1 << args.log_blowup, nsteps, sum(lde) / len(lde), sum(mt) / len(mt)),
+        "seconds_per_step": t, "sample_cols": c,
+        "poseidon_hash_per_s": perms_per_commit(n_ext, c) / (sum(mt) / len(mt)),
+    }
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    base = run_cpu_baseline(args, budget_s=150.0, nsteps=max(1, args.steps), warmup=max(0, min(args.warmup, 1)))
+    line = {
+        "impl": "reference", "metric": "LDE+Merkle commit throughput (2^%d x %d, blowup %d)" % (args.log_rows, args.cols, 1 << args.log_blowup),
+        "value": base["value"], "unit": "Melem/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": base["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic",
+        "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d, extendPol + merkletree (CPU sample: %d cols)"
+                               % (args.log_rows, args.cols, args.log_rows + args.log_blowup, base["sample_cols"])},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": base["value"], "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "poseidon_hash_per_s": base["poseidon_hash_per_s"], "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# --------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------
+def verify_full_size(ctx, torch, ext_t, tree_t, n, n_ext, ncols, col0, ncols_local, rows0, nrows_local):
+    """Spot-check parity at full size against the oracle (outside the timed region):
+    two whole columns of the extension, and Merkle paths of sampled leaves up to the root."""
+    from oracle import refbind
+    from xlayer_prover_b200._capi import synth_matrix
+    orc = refbind.best()
+    out = {}
+    if ext_t is not None and rows0 == 0 and nrows_local == n_ext:
+        cols = sorted(set([0, ncols_local - 1]))
+        a = np.concatenate([synth_matrix(n, 1, SEED, col0=col0 + c, ncols_total=ncols) for c in cols], axis=1)
+        want = orc.extend_pol(a, n_ext)
+        got = ext_t.view(n_ext, ncols_local)[:, cols].cpu().numpy().view(np.uint64)
+        out["lde_columns_checked"] = [col0 + c for c in cols]
+        out["lde_columns_equal"] = bool(np.array_equal(got, want))
+    if tree_t is not None and ext_t is not None and ncols_local == ncols:
+        tree = tree_t.cpu().numpy().view(np.uint64)
+        depth = n_ext.bit_length() - 1
+        ok = True
+        rng = np.random.default_rng(1)
+        for idx in [0, n_ext - 1] + [int(x) for x in rng.integers(0, n_ext, size=14)]:
+            row = ext_t.view(n_ext, ncols)[idx].cpu().numpy().view(np.uint64)
+            h = orc.linear_hash(row)
+            ok &= bool(np.array_equal(h, tree[4 * idx: 4 * idx + 4]))
+            off, nn, i = 0, n_ext, idx
+            for _ in range(depth):
+                sib = tree[off + 4 * (i ^ 1): off + 4 * (i ^ 1) + 4]
+                pair = np.concatenate([h, sib]) if i % 2 == 0 else np.concatenate([sib, h])
+                h = orc.hash_full_result(np.concatenate([pair, np.zeros(4, dtype=np.uint64)]))[:4]
+                off += 4 * nn
+                nn //= 2
+                i //= 2
+            ok &= bool(np.array_equal(h, tree[-4:]))
+        out["merkle_paths_checked"] = 16
+        out["merkle_paths_equal"] = ok
+    out["oracle"] = "reference build" if refbind.reference() else "C port"
+    return out
+
+
+def main_ours(args):
+    import torch
+    import torch.distributed as dist
+    from xlayer_prover_b200 import Context, tree_num_elements
+    from xlayer_prover_b200.sharded import ShardedCommit
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        if args.gpus > 1:
+            sys.stderr.write("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d\n" % (args.gpus, args.gpus))
+            return 2
+    if not torch.cuda.is_available():
+        sys.stderr.write("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)\n")
+        return 2
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n, n_ext, C = 1 << args.log_rows, 1 << (args.log_rows + args.log_blowup), args.cols
+    K, W = args.steps, args.warmup
+    ctx = Context(local_rank)
+    stream = torch.cuda.Stream(device=dev)
+    ctx.set_stream(stream.cuda_stream)
+    hbm_peak, peak_src = measured_peaks()
+    int_peak = ctx.measure_int_peak()
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    result = {}
+    with torch.cuda.stream(stream):
+        sc = ShardedCommit(ctx, n, n_ext, C, device=dev) if world > 1 else None
+        c0, w = (sc.c0, sc.w) if sc else (0, C)
+        # ---- inputs resident in HBM (generated on the device, identical for every N) ----
+        din = torch.empty(max(1, n * w), dtype=torch.int64, device=dev)
+        ctx.synth_fill(din, n, w, SEED, col0=c0, ncols_total=C)
+        if sc is None:
+            dext = torch.empty(n_ext * C, dtype=torch.int64, device=dev)
+            dtree = torch.empty(tree_num_elements(n_ext), dtype=torch.int64, device=dev)
+
+        def step():
+            if sc is None:
+                return ctx.commit(dext, dtree, din, n, n_ext, C)
+            return sc.commit(din)
+
+        for _ in range(W):
+            step()
+        ctx.get_profile()
+        barrier()
+        launches0 = ctx.launch_count()
+        ctx.set_profiling(True)
+        sampler = ClockSampler(local_rank)
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        root = None
+        for _ in range(K):
+            root = step()
+        e1.record(stream)
+        barrier()
+        clocks = sampler.stop()
+        ctx.set_profiling(False)
+        prof = ctx.get_profile()
+        launches = ctx.launch_count() - launches0
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        ms_per_step = float(ms.item()) / K
+        result.update(ms_per_step=ms_per_step, launches=launches, prof=prof, clocks=clocks,
+                      root=[int(x) for x in (root.cpu().numpy().view(np.uint64) if hasattr(root, "cpu") else root)] if root is not None else None)
+
+        # ---- parity spot-check at full size (untimed) ----
+        verify = None
+        if not args.no_verify and rank == 0:
+            try:
+                if sc is None:
+                    verify = verify_full_size(ctx, torch, dext, dtree, n, n_ext, C, 0, C, 0, n_ext)
+                else:
+                    verify = {"note": "N>1: root compared with the N=1 root by the caller; tree assembled on rank 0"}
+            except Exception as ex:                                     # never let the checker hide the measurement
+                verify = {"error": repr(ex)}
+        result["verify"] = verify
+
+        # ---- e2e: host buffers through the C ABI ----
+        e2e = None
+        if not args.no_e2e:
+            if sc is None:
+                del dext, dtree, din
+            torch.cuda.empty_cache()
+            try:
+                e2e = run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c0, w, barrier)
+            except Exception as ex:                                     # keep the device-resident measurement
+                e2e = {"value": None, "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "note": "failed: %r" % (ex,)}
+        result["e2e"] = e2e
+
+    if rank == 0:
+        perms = perms_per_commit(n_ext, C)
+        sec = result["ms_per_step"] / 1e3
+        prof = result["prof"]
+        leaf_ms = prof["leaf_hash"][0] / max(1, prof["leaf_hash"][1])
+        R = n_ext // world
+        leaf_bytes = 8.0 * C * R + 32.0 * R                              # algorithmic bytes of one leaf-hash launch
+        leaf_gbs = leaf_bytes / (leaf_ms * 1e-3) / 1e9 if leaf_ms > 0 else None
+        leaf_perms = R * ((C + 7) // 8)
+        lde_ms = (prof["intt"][0] + prof["ntt_ext"][0]) / K
+        wcols = w
+        lde_bytes = 8.0 * wcols * (n + n_ext)
+        line = {
+            "metric": "LDE+Merkle commit throughput (2^%d x %d, blowup %d)" % (args.log_rows, C, 1 << args.log_blowup),
+            "value": n * C / sec / 1e6, "unit": "Melem/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": result["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
+                                   % (args.log_rows, C, args.log_rows + args.log_blowup),
+                       "l2_policy": "inputs (%.1f GB) far larger than the 126 MB L2; no flush needed" % (8.0 * n * C / 1e9),
+                       "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d -> NCCL all-to-all -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
+                       "seed": hex(SEED)},
+            "commit_ms": result["ms_per_step"], "poseidon_hash_per_s": perms / sec,
+            "stage_ms": {"intt": prof["intt"][0] / K, "ntt_ext": prof["ntt_ext"][0] / K, "leaf_hash": prof["leaf_hash"][0] / K,
+                         "tree_levels": prof["tree_levels"][0] / K, "note": "rank 0, per step, CUDA events on the launching stream"},
+            "roofline": {"kernel": "k_linear_hash_rows", "bound": "hbm", "achieved": leaf_gbs, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": (leaf_gbs / hbm_peak) if leaf_gbs else None, "traffic": None, "peak_source": peak_src,
+                         "launch_ms": leaf_ms, "algorithmic_bytes_per_launch": leaf_bytes,
+                         "note": "dominant kernel by time; it is integer-issue bound, not HBM bound -- see roofline_int"},
+            "roofline_int": {"kernel": "k_linear_hash_rows", "bound": "integer issue (IMAD + IADD3 pipes)",
+                             "achieved": leaf_perms * SASS_INSTR_PER_PERM / (leaf_ms * 1e-3) if leaf_ms > 0 else None,
+                             "peak": int_peak["interleaved_lane_ops_per_s"], "unit": "lane-instr/s",
+                             "frac": (leaf_perms * SASS_INSTR_PER_PERM / (leaf_ms * 1e-3) / int_peak["interleaved_lane_ops_per_s"]) if leaf_ms > 0 else None,
+                             "instr_per_permutation": SASS_INSTR_PER_PERM, "measured_peaks": int_peak,
+                             "leaf_hash_perm_per_s": leaf_perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None},
+            "roofline_lde": {"kernels": "k_ntt_tile x4 passes per column block", "bound": "hbm", "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms > 0 else None,
+                             "peak": hbm_peak, "unit": "GB/s", "frac": (lde_bytes / (lde_ms * 1e-3) / 1e9 / hbm_peak) if lde_ms > 0 else None,
+                             "algorithmic_bytes": lde_bytes, "design_traffic_bytes": 8.0 * wcols * (5 * n + 3 * n_ext), "lde_ms": lde_ms},
+            "clocks": result["clocks"], "gpu_launches": result["launches"], "e2e": result["e2e"],
+            "root": ["%#018x" % x for x in result["root"]] if result["root"] else None, "verify": result["verify"],
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                base = run_cpu_baseline(args, args.cpu_budget_s)
+                line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            except Exception as ex:
+                line["cpu_baseline"] = {"error": repr(ex)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    ctx.close()
+    return 0
+
+
+def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c0, w, barrier):
+    """Same commit, host buffers: per step H2D of this rank's trace columns and D2H of its extended rows +
+    (rank 0) every Merkle node, all inside the timed region."""
+    from xlayer_prover_b200 import tree_num_elements
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = 64 << 30
+    K, W = args.steps, args.warmup
+    R = n_ext // world
+    in_bytes, ext_bytes, tree_bytes = 8 * n * w, 8 * R * C, 8 * tree_num_elements(n_ext)
+    need = (in_bytes + ext_bytes) * (world if world > 1 else 1) + tree_bytes
+    full = need < 0.8 * avail
+    note = "H2D trace, D2H extended matrix + all Merkle nodes + root"
+    if not full:
+        need = in_bytes * (world if world > 1 else 1) + tree_bytes
+        if need > 0.8 * avail:
+            return {"value": None, "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                    "note": "skipped: host has %.0f GB available, needs %.0f GB of pinned memory" % (avail / 1e9, need / 1e9)}
+        note = "host RAM too small to pin the %.0f GB extended matrix: H2D trace, D2H Merkle nodes + root only" % (ext_bytes * world / 1e9)
+    # pinned host buffers straight from cudaHostAlloc (torch's pinned allocator rounds sizes up to a power of two)
+    import ctypes
+
+    def pinned(nwords):
+        p = ctx.host_alloc(8 * max(1, nwords))
+        t = torch.frombuffer((ctypes.c_char * (8 * max(1, nwords))).from_address(p), dtype=torch.int64)
+        return p, t
+    hin_p, hin = pinned(n * w)
+    hext_p, hext = pinned(R * C) if full else (None, None)
+    htree_p, htree = pinned(tree_num_elements(n_ext)) if rank == 0 else (None, None)
+    # fill the pinned input (device generator -> host), then drop the device copy
+    tmp = torch.empty(max(1, n * w), dtype=torch.int64, device=dev)
+    ctx.synth_fill(tmp, n, w, SEED, col0=c0, ncols_total=C)
+    ctx.memcpy(hin_p, tmp, 8 * n * w)
+    del tmp
+    torch.cuda.empty_cache()
+
+    if sc is None:
+        def step():
+            return ctx.commit(hext_p, htree_p, hin_p, n, n_ext, C)
+    else:
+        din = torch.empty(max(1, n * w), dtype=torch.int64, device=dev)
+
+        def step():
+            din.copy_(hin, non_blocking=True)
+            root = sc.commit(din)
+            if hext is not None:
+                hext.copy_(sc.slab, non_blocking=True)
+            if rank == 0:
+                htree.copy_(sc.tree, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return root
+    for _ in range(min(W, 3)):
+        step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        step()
+    barrier()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    sec = float(dt.item()) / K
+    for p in (hin_p, hext_p, htree_p):
+        if p:
+            ctx.host_free(p)
+    return {"value": n * C / sec / 1e6, "unit": "Melem/s", "ms_per_step": sec * 1e3,
+            "h2d_bytes_per_step": 8 * n * C, "d2h_bytes_per_step": (8 * n_ext * C if full else 0) + tree_bytes + 32,
+            "note": note, "pinned": True}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

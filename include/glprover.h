@@ -115,6 +115,17 @@ int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2])
  * results for the host to compare against the oracle: out[5*i..] = add, sub, mul, mul_pow2(a, b%96), canon */
 int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t n, uint64_t *out);
 
+/* ---- measurement hooks (bench.py) ---- */
+/* When on, the NTT and Merkle stages are bracketed by CUDA events on the context's stream. */
+int glp_set_profiling(glp_ctx *ctx, int on);
+/* Synchronises, then returns and clears the accumulated stage times in milliseconds and launch counts:
+ * ms[0] inverse NTT (+coset scale), ms[1] forward NTT, ms[2] leaf hash (linear_hash rows), ms[3] tree levels;
+ * count[i] = number of bracketed intervals summed into ms[i]. */
+int glp_get_profile(glp_ctx *ctx, float ms[4], uint32_t count[4]);
+/* Dependent-free integer micro-benchmarks on this device: ops_per_s[0] = IMAD (32-bit multiply-add, the IMAD.WIDE pipe) lane-ops/s,
+ * [1] = 32-bit add lane-ops/s (two adds fused as IADD3 count as one), [2] = both interleaved (sum of lane-ops/s). */
+int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3]);
+
 #ifdef __cplusplus
 }
 #endif

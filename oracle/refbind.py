@@ -69,6 +69,8 @@ class _Lib:
     # ---- NTT
     def ntt(self, src, inverse=False, extend=False, nphase=3, nblock=1):
         src = np.ascontiguousarray(src, dtype=np.uint64)
+        if src.size == 0:
+            return src.copy()
         a = src.reshape(src.shape[0], -1) if src.ndim > 1 else src.reshape(-1, 1)
         size, ncols = a.shape
         dst = np.zeros_like(a)

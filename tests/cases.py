@@ -1,0 +1,165 @@
+"""Inputs and checks shared by the emulator tests (CPU) and the GPU parity tests.
+
+The generators restate the input loops of the reference's own tests
+(src/goldilocks/tests/tests.cpp: Fibonacci vectors :1597-1610, :1747-1760; column-Fibonacci matrices
+:1817-1835, :2260-2275) so the known answers in tests/golden/kat.json apply."""
+import numpy as np
+
+P = 0xFFFFFFFF00000001
+
+
+def fib_vector(n, a0=0, a1=1):
+    v = [a0 % P, a1 % P]
+    for _ in range(2, n):
+        v.append((v[-1] + v[-2]) % P)
+    return np.array(v[:n], dtype=np.uint64)
+
+
+def fib_matrix(nrows, ncols):
+    """rows 0 and 1 are 1..ncols, row j = row j-1 + row j-2 (tests.cpp:1821-1835, :2260-2275)."""
+    m = np.zeros((nrows, ncols), dtype=object)
+    for i in range(ncols):
+        m[0, i] = i + 1
+        if nrows > 1:
+            m[1, i] = i + 1
+    for j in range(2, nrows):
+        m[j] = (m[j - 1] + m[j - 2]) % P
+    return m.astype(np.uint64)
+
+
+def edge_matrix(rng, nrows, ncols):
+    """uniform words over the whole u64 range (so ~2^-32 of them are non-canonical) plus the boundary values"""
+    x = rng.integers(0, 2 ** 64, size=(nrows, ncols), dtype=np.uint64)
+    flat = x.reshape(-1)
+    edges = np.array([P - 1, P, P + 1, 2 ** 64 - 1, 0, 1], dtype=np.uint64)
+    k = min(flat.size, edges.size)
+    flat[:k] = edges[:k]
+    return x
+
+
+def tree_words(nrows):
+    return (2 * nrows - 1) * 4 if nrows else 0
+
+
+def monomial_columns(n, degrees, w_n):
+    """column c = evaluations of x^degrees[c] on the size-n subgroup: in[i,c] = w_n^(i*deg)"""
+    out = np.zeros((n, len(degrees)), dtype=np.uint64)
+    for c, d in enumerate(degrees):
+        g = pow(w_n, d, P)
+        v = 1
+        for i in range(n):
+            out[i, c] = v
+            v = v * g % P
+    return out
+
+
+def check_equal(got, want, what=""):
+    got = np.asarray(got).reshape(-1)
+    want = np.asarray(want).reshape(-1)
+    assert got.shape == want.shape, (what, got.shape, want.shape)
+    if not np.array_equal(got, want):
+        bad = np.nonzero(got != want)[0]
+        raise AssertionError("%s: %d of %d words differ; first at %d: got %#x want %#x"
+                             % (what, bad.size, got.size, bad[0], int(got[bad[0]]), int(want[bad[0]])))
+
+
+# ---------------------------------------------------------------------------------------------
+# parity checks against an oracle, for any Context (real library on the GPU, or the emulator build)
+# ---------------------------------------------------------------------------------------------
+def run_ntt(ctx, a, inverse=False, extend=False, device=False, inplace=False):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    n, c = a.shape
+    if device:
+        src = ctx.to_device(a)
+        dst = src if inplace else ctx.device_alloc(max(a.nbytes, 8))
+        ctx.ntt(dst, src, n, c, inverse, extend)
+        out = ctx.to_host(dst, a.shape)
+        ctx.device_free(src)
+        if not inplace:
+            ctx.device_free(dst)
+        return out
+    if inplace:
+        buf = a.copy()
+        ctx.ntt(None, buf, n, c, inverse, extend)
+        return buf
+    out = np.zeros_like(a)
+    ctx.ntt(out, a, n, c, inverse, extend)
+    return out
+
+
+def check_ntt(ctx, oracle, a, **kw):
+    for inv, ext in [(False, False), (True, False), (True, True)]:
+        check_equal(run_ntt(ctx, a, inv, ext, **kw), oracle.ntt(a, inverse=inv, extend=ext),
+                    "ntt %s inv=%d ext=%d %s" % (a.shape, inv, ext, kw))
+
+
+def run_extend(ctx, a, n_ext, device=False, alias=False):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    n, c = a.shape
+    if alias:                                   # output aliases input (tests.cpp:2578)
+        buf = np.zeros((n_ext, c), dtype=np.uint64)
+        buf.reshape(-1)[: n * c] = a.reshape(-1)
+        if device:
+            d = ctx.to_device(buf)
+            ctx.extend_pol(d, d, n_ext, n, c)
+            out = ctx.to_host(d, buf.shape)
+            ctx.device_free(d)
+            return out
+        ctx.extend_pol(buf, buf, n_ext, n, c)
+        return buf
+    if device:
+        src = ctx.to_device(a)
+        dst = ctx.device_alloc(n_ext * c * 8)
+        ctx.extend_pol(dst, src, n_ext, n, c)
+        out = ctx.to_host(dst, (n_ext, c))
+        ctx.device_free(src)
+        ctx.device_free(dst)
+        return out
+    out = np.zeros((n_ext, c), dtype=np.uint64)
+    ctx.extend_pol(out, a, n_ext, n, c)
+    return out
+
+
+def run_merkletree(ctx, a, nrows=None, ncols=None, device=False, dim=1):
+    if a is not None:
+        a = np.ascontiguousarray(a, dtype=np.uint64)
+        nrows, width = a.shape
+        ncols = width // dim
+    tree = np.zeros(tree_words(nrows), dtype=np.uint64)
+    if device and a is not None and a.size:
+        src = ctx.to_device(a)
+        dt = ctx.device_alloc(max(tree.nbytes, 8))
+        ctx.merkletree(dt, src, ncols, nrows, dim)
+        tree = ctx.to_host(dt, tree.shape)
+        ctx.device_free(src)
+        ctx.device_free(dt)
+    else:
+        ctx.merkletree(tree, a if (a is not None and a.size) else None, ncols, nrows, dim)
+    return tree
+
+
+def run_commit(ctx, a, n_ext, device=False):
+    a = np.ascontiguousarray(a, dtype=np.uint64)
+    n, c = a.shape
+    if device:
+        src = ctx.to_device(a)
+        dext = ctx.device_alloc(n_ext * c * 8)
+        dtree = ctx.device_alloc(tree_words(n_ext) * 8)
+        root = ctx.commit(dext, dtree, src, n, n_ext, c)
+        ext, tree = ctx.to_host(dext, (n_ext, c)), ctx.to_host(dtree, (tree_words(n_ext),))
+        for p in (src, dext, dtree):
+            ctx.device_free(p)
+        return ext, tree, root
+    ext = np.zeros((n_ext, c), dtype=np.uint64)
+    tree = np.zeros(tree_words(n_ext), dtype=np.uint64)
+    root = ctx.commit(ext, tree, a, n, n_ext, c)
+    return ext, tree, root
+
+
+def check_commit(ctx, oracle, a, n_ext, **kw):
+    ext, tree, root = run_commit(ctx, a, n_ext, **kw)
+    want_ext = oracle.extend_pol(a, n_ext)
+    want_tree = oracle.merkletree(want_ext)
+    check_equal(ext, want_ext, "commit ext %s" % (a.shape,))
+    check_equal(tree, want_tree, "commit tree %s" % (a.shape,))
+    check_equal(root, want_tree[-4:], "commit root")

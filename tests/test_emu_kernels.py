@@ -1,0 +1,129 @@
+"""Kernel-logic tests on the CPU: the SAME .cu/.cuh sources compiled with -DGLP_EMU against
+tests/cuemu (host threads stand in for CUDA threads) and compared with the oracle at tiny sizes.
+This exercises index arithmetic, pass planning (1/2/3 tile passes), staging and the C ABI's argument
+handling here, where there is no GPU; the inline-PTX paths are only checked on the B200 (-m gpu).
+The emulator library is test infrastructure: the package never loads it."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from cases import (P, check_commit, check_equal, check_ntt, edge_matrix, fib_matrix, fib_vector, run_extend,
+                   run_merkletree, tree_words)
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+EMU = os.path.join(HERE, "cuemu", "libglprover_emu.so")
+
+
+@pytest.fixture(scope="module")
+def emu_lib():
+    subprocess.run([os.path.join(HERE, "cuemu", "build_emu.sh")], check=True, capture_output=True)
+    from xlayer_prover_b200._capi import GlpLib
+    return GlpLib(EMU)
+
+
+def make_ctx(lib, max_logq=None):
+    from xlayer_prover_b200._capi import Context
+    old = os.environ.get("GLP_NTT_MAX_LOGQ")
+    if max_logq is not None:
+        os.environ["GLP_NTT_MAX_LOGQ"] = str(max_logq)
+    try:
+        return Context(0, lib)
+    finally:
+        if old is None:
+            os.environ.pop("GLP_NTT_MAX_LOGQ", None)
+        else:
+            os.environ["GLP_NTT_MAX_LOGQ"] = old
+
+
+@pytest.fixture(scope="module")
+def ectx(emu_lib):
+    c = make_ctx(emu_lib)
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def ectx3(emu_lib):
+    """tile size capped at 2^3 rows so 64- and 512-row transforms take the 2- and 3-pass paths"""
+    c = make_ctx(emu_lib, 3)
+    yield c
+    c.close()
+
+
+def test_poseidon(ectx, golden, fixtures):
+    out = np.zeros(12, dtype=np.uint64)
+    ectx.hash_full_result(out, fib_vector(12), 1)
+    check_equal(out, golden["poseidon_fibonacci"]["out"])
+    outs = np.zeros_like(fixtures["perm_in"])
+    ectx.hash_full_result(outs, fixtures["perm_in"], outs.shape[0])
+    check_equal(outs, fixtures["perm_out"])
+
+
+def test_linear_hash_and_tree(ectx, oracle, golden, fixtures, rng):
+    out = np.zeros(4, dtype=np.uint64)
+    ectx.linear_hash_rows(out, fib_vector(128), 128, 128, 1)
+    check_equal(out, golden["linear_hash_fibonacci128"]["out"])
+    check_equal(run_merkletree(ectx, fib_matrix(64, 128))[-4:], golden["merkletree_64x128_root"]["out"])
+    check_equal(run_merkletree(ectx, None, 64, 0)[-4:], golden["merkletree_64x0_root"]["out"])
+    for k in ("mt_32x13", "mt_16x4", "mt_16x3", "mt_8x8", "mt_4x660", "mt_1x9"):
+        for dev in (False, True):
+            check_equal(run_merkletree(ectx, fixtures[k + "_in"], device=dev), fixtures[k + "_tree"], k)
+    a = edge_matrix(rng, 8, 15)
+    check_equal(run_merkletree(ectx, a, dim=3), oracle.merkletree(a), "dim=3")
+
+
+def test_ntt_single_pass(ectx, oracle, fixtures, rng):
+    for n, c in [(1, 3), (2, 3), (4, 1), (16, 8), (32, 5), (128, 2)]:
+        check_ntt(ectx, oracle, edge_matrix(rng, n, c))
+    check_ntt(ectx, oracle, edge_matrix(rng, 64, 3), device=True, inplace=True)
+    check_ntt(ectx, oracle, edge_matrix(rng, 16, 2), inplace=True)
+    check_equal(run_extend(ectx, fixtures["ntt_2x3_in"], 2), oracle.extend_pol(fixtures["ntt_2x3_in"], 2))
+
+
+def test_ntt_two_and_three_passes(ectx3, oracle, rng):
+    for n, c in [(16, 3), (64, 5), (128, 1), (512, 2)]:
+        check_ntt(ectx3, oracle, edge_matrix(rng, n, c))
+    check_ntt(ectx3, oracle, edge_matrix(rng, 64, 2), device=True, inplace=True)
+
+
+def test_extend_pol(ectx, ectx3, golden, fixtures, port):
+    for c in (ectx, ectx3):
+        check_equal(run_extend(c, fib_matrix(16, 8), 32)[:, 0], golden["extendpol_16x8_to_32_col0"]["out"])
+        check_equal(run_extend(c, fib_matrix(16, 8), 32, alias=True)[:, 0], golden["extendpol_16x8_to_32_col0"]["out"])
+        for k in ("ext_64x5_b4", "ext_32x16_b8", "ext_1x4_b2"):
+            check_equal(run_extend(c, fixtures[k + "_in"], fixtures[k + "_out"].shape[0]), fixtures[k + "_out"], k)
+    # N_ext = 4 makes the reference assert (ntt_goldilocks.cpp:302); the maths is well defined, check the port
+    a = fixtures["ntt_2x3_in"]
+    check_equal(run_extend(ectx, a, 4), port.extend_pol(a, 4))
+
+
+def test_commit_host_and_device(ectx3, oracle, fixtures):
+    a = fixtures["commit_64x9_in"]
+    ectx3.set_scratch_limit((128 + 64) * 8 * 4 * 2)          # 4-column blocks: exercises the streamed upload path
+    check_commit(ectx3, oracle, a, 128)
+    check_commit(ectx3, oracle, a, 128, device=True)
+    ectx3.set_scratch_limit(0)
+    ext = fixtures["commit_64x9_ext"]
+    tree = fixtures["commit_64x9_tree"]
+    proof = np.zeros(9 + 4 * 7, dtype=np.uint64)
+    ectx3.merkle_group_proof(proof, ext, tree, 9, 128, 77)
+    check_equal(proof, fixtures["commit_64x9_proof_77"])
+
+
+def test_argument_errors(ectx):
+    from xlayer_prover_b200._capi import GLP_E_ARG, GLP_E_DOMAIN, GlpError
+    a = np.zeros((12, 2), dtype=np.uint64)
+    with pytest.raises(GlpError) as e:
+        ectx.ntt(a, a, 12, 2)
+    assert e.value.code == GLP_E_ARG
+    with pytest.raises(GlpError) as e:
+        ectx.ntt(a, a, 1 << 33, 1)
+    assert e.value.code == GLP_E_DOMAIN
+    with pytest.raises(GlpError) as e:
+        ectx.merkletree(np.zeros(100, dtype=np.uint64), a, 2, 12)
+    assert e.value.code == GLP_E_ARG
+    ectx.ntt(a, a, 0, 2)          # no-ops, as the reference (ntt_goldilocks.cpp:168-171)
+    ectx.ntt(a, a, 4, 0)
+    ectx.merkletree(a, a, 2, 0)

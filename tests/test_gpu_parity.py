@@ -1,0 +1,401 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (ctypes -> libglprover.so) on a B200, against
+the oracle (the compiled reference when oracle/_ref travelled with the snapshot, else the pinned C port),
+the reference's own known answers (tests/golden/kat.json) and the reference-generated fixtures.
+
+Bit-exact means equal after Goldilocks::toU64 canonicalisation, for every extended element and every Merkle
+node: the library emits canonical words, the oracle side is canonicalised by refbind."""
+import os
+
+import numpy as np
+import pytest
+
+from cases import (P, check_commit, check_equal, check_ntt, edge_matrix, fib_matrix, fib_vector, monomial_columns,
+                   run_commit, run_extend, run_merkletree, run_ntt, tree_words)
+
+pytestmark = pytest.mark.gpu
+
+
+def env_ctx(**env):
+    from xlayer_prover_b200 import Context
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update({k: str(v) for k, v in env.items()})
+    try:
+        return Context(0)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+# ---------------------------------------------------------------- field (PTX paths)
+def test_field_primitives(ctx, rng):
+    edges = np.array([0, 1, 2, P - 2, P - 1, P, P + 1, 2 ** 64 - 1, 2 ** 64 - 2, 2 ** 32 - 1, 2 ** 32, 2 ** 32 + 1,
+                      2 ** 63, 0xFFFFFFFF, 0xFFFFFFFF00000000, 0xFFFFFFFEFFFFFFFF], dtype=np.uint64)
+    a = np.concatenate([np.repeat(edges, edges.size), rng.integers(0, 2 ** 64, size=1 << 16, dtype=np.uint64)])
+    b = np.concatenate([np.tile(edges, edges.size), rng.integers(0, 2 ** 64, size=1 << 16, dtype=np.uint64)])
+    # shift amounts 0..95 all get exercised through b % 96
+    b[edges.size ** 2: edges.size ** 2 + 96] = np.arange(96, dtype=np.uint64)
+    got = ctx.field_selftest(a, b)
+    ai = [int(x) for x in a]
+    bi = [int(x) for x in b]
+    want = np.array([[(x + y) % P, (x - y) % P, (x * y) % P, (x * pow(2, y % 96, P)) % P, x % P] for x, y in zip(ai, bi)],
+                    dtype=np.uint64)
+    check_equal(got, want, "field selftest")
+
+
+# ---------------------------------------------------------------- Poseidon
+def test_poseidon_kats(ctx, golden, fixtures):
+    out = np.zeros(12, dtype=np.uint64)
+    ctx.hash_full_result(out, fib_vector(12), 1)
+    check_equal(out, golden["poseidon_fibonacci"]["out"], "tests.cpp poseidon_full_seq")
+    ctx.hash_full_result(out, np.zeros(12, dtype=np.uint64), 1)
+    check_equal(out, golden["poseidon_zero"]["out"], "tests.cpp poseidon_full_seq zero")
+    outs = np.zeros_like(fixtures["perm_in"])
+    ctx.hash_full_result(outs, fixtures["perm_in"], outs.shape[0])
+    check_equal(outs, fixtures["perm_out"])
+
+
+def test_poseidon_random_vs_oracle(ctx, oracle, rng):
+    x = edge_matrix(rng, 4096, 12)
+    out = np.zeros_like(x)
+    ctx.hash_full_result(out, x, x.shape[0])
+    for i in rng.integers(0, 4096, size=64):
+        check_equal(out[i], oracle.hash_full_result(x[i]), "perm %d" % i)
+    check_equal(out[0], oracle.hash_full_result(x[0]), "perm with boundary words")
+
+
+def test_linear_hash_kat_and_sizes(ctx, oracle, golden, rng):
+    out = np.zeros(4, dtype=np.uint64)
+    ctx.linear_hash_rows(out, fib_vector(128), 128, 128, 1)
+    check_equal(out, golden["linear_hash_fibonacci128"]["out"], "tests.cpp linear_hash_seq")
+    for size in list(range(1, 20)) + [24, 25, 100, 128, 660, 665, 751]:
+        a = edge_matrix(rng, 37, size + 3)              # pitch > ncols
+        got = np.zeros((37, 4), dtype=np.uint64)
+        ctx.linear_hash_rows(got, a, size, size + 3, 37)
+        check_equal(got, oracle.linear_hash_rows(np.ascontiguousarray(a[:, :size])), "linear_hash size %d" % size)
+
+
+def test_merkletree_kats(ctx, golden):
+    check_equal(run_merkletree(ctx, fib_matrix(64, 128))[-4:], golden["merkletree_64x128_root"]["out"], "64x128")
+    check_equal(run_merkletree(ctx, fib_matrix(64, 128), device=True)[-4:], golden["merkletree_64x128_root"]["out"], "64x128 dev")
+    check_equal(run_merkletree(ctx, None, 64, 0)[-4:], golden["merkletree_64x0_root"]["out"], "64x0")
+    check_equal(run_merkletree(ctx, None, 1 << 17, 0)[-4:], golden["merkletree_131072x0_root"]["out"], "2^17x0")
+
+
+def test_merkletree_fixtures(ctx, fixtures):
+    for k in ("mt_32x13", "mt_16x4", "mt_16x3", "mt_8x8", "mt_4x660", "mt_1x9"):
+        for dev in (False, True):
+            check_equal(run_merkletree(ctx, fixtures[k + "_in"], device=dev), fixtures[k + "_tree"], k)
+
+
+@pytest.mark.parametrize("ncols", [1, 3, 4, 5, 8, 9, 12, 16, 100, 128, 660, 665, 751])
+def test_merkletree_every_node(ctx, oracle, rng, ncols):
+    for nrows in (1, 2, 8, 512):
+        a = edge_matrix(rng, nrows, ncols)
+        check_equal(run_merkletree(ctx, a, device=(nrows == 512)), oracle.merkletree(a), "tree %dx%d" % (nrows, ncols))
+
+
+def test_merkletree_wide_tree_and_dim(ctx, oracle, rng):
+    a = edge_matrix(rng, 1 << 14, 24)                   # exercises the per-level kernels and the single-CTA top
+    check_equal(run_merkletree(ctx, a, device=True), oracle.merkletree(a), "2^14 x 24")
+    a = edge_matrix(rng, 64, 36)
+    check_equal(run_merkletree(ctx, a, dim=3), oracle.merkletree(a), "dim=3 (FRI trees, friProve.cpp:120)")
+
+
+# ---------------------------------------------------------------- NTT
+def test_ntt_reference_roundtrips(ctx):
+    """tests.cpp ntt / ntt_block: NTT then INTT returns the input for every dst/src combination"""
+    from xlayer_prover_b200 import NTT_Goldilocks
+    g = NTT_Goldilocks(16, ctx=ctx)
+    a = fib_vector(16, 1, 1).reshape(16, 1).copy()
+    init = a.copy()
+    for _ in range(5):
+        g.NTT(a, a, 16)
+        g.INTT(a, a, 16)
+    check_equal(a, init, "ntt")
+    a = fib_matrix(16, 8)
+    init = a.copy()
+    for _ in range(5):                                  # option 1: dst NULL
+        g.NTT(None, a, 16, 8)
+        g.INTT(None, a, 16, 8)
+    check_equal(a, init, "dst=NULL")
+    dst = np.zeros_like(a)
+    for _ in range(5):                                  # option 3: dst != src
+        g.NTT(dst, a, 16, 8)
+        a[:] = 0
+        g.INTT(a, dst, 16, 8)
+    check_equal(a, init, "dst!=src")
+    for _ in range(5):                                  # options 4/5: phases and blocks, also out of range
+        g.NTT(a, a, 16, 8, None, 3, 5)
+        g.INTT(a, a, 16, 8, None, 4, 3)
+        g.NTT(a, a, 16, 8, None, 3, 3000)
+        g.INTT(a, a, 16, 8, None, 4, -1)
+    check_equal(a, init, "phases/blocks")
+    a1 = np.array([[1, 2, 3]], dtype=np.uint64)         # size 1
+    b1 = np.zeros_like(a1)
+    g.NTT(b1, a1, 1, 3)
+    check_equal(b1, a1)
+    g.INTT(a1, b1, 1, 3)
+    check_equal(a1, [1, 2, 3])
+    a2 = np.array([[1, 2, 3], [4, 5, 6]], dtype=np.uint64)   # size 2
+    b2 = np.zeros_like(a2)
+    g.NTT(b2, a2, 2, 3)
+    g.INTT(a2, b2, 2, 3)
+    check_equal(a2, [1, 2, 3, 4, 5, 6])
+    g.NTT(b2, a2, 0, 3)                                 # size 0 / ncols 0 do not crash
+    g.INTT(a2, b2, 1, 0)
+    assert NTT_Goldilocks(0).s == 0                     # inert object (starks.hpp:81-82 when !generateProof)
+
+
+@pytest.mark.parametrize("logn", list(range(0, 15)))
+def test_ntt_vs_oracle_all_sizes(ctx, oracle, rng, logn):
+    for c in (1, 3, 8):
+        check_ntt(ctx, oracle, edge_matrix(rng, 1 << logn, c))
+    check_ntt(ctx, oracle, edge_matrix(rng, 1 << logn, 5), device=True, inplace=True)
+
+
+def test_ntt_fixtures(ctx, fixtures):
+    for k in ("ntt_128x3", "ntt_2x3", "ntt_1024x1"):
+        a = fixtures[k + "_in"]
+        check_equal(run_ntt(ctx, a), fixtures[k + "_fwd"], k)
+        check_equal(run_ntt(ctx, a, True), fixtures[k + "_inv"], k)
+        check_equal(run_ntt(ctx, a, True, True), fixtures[k + "_invext"], k)
+
+
+def test_ntt_two_pass_large(ctx, oracle, rng):
+    for n, c in [(1 << 16, 3), (1 << 18, 2), (1 << 20, 1)]:
+        a = edge_matrix(rng, n, c)
+        check_equal(run_ntt(ctx, a, device=True), oracle.ntt(a), "ntt %dx%d" % (n, c))
+        check_equal(run_ntt(ctx, a, True, True, device=True), oracle.ntt(a, inverse=True, extend=True), "intt-ext %dx%d" % (n, c))
+
+
+def test_ntt_three_pass_and_cb2(ctx, oracle, rng):
+    """the 3-pass plan (sizes above 2^24 in production) reached at small sizes by capping the tile; and the
+    2-column tile variant"""
+    for env in ({"GLP_NTT_MAX_LOGQ": 5}, {"GLP_NTT_CB": 2}, {"GLP_NTT_CB": 2, "GLP_NTT_MAX_LOGQ": 4}):
+        c = env_ctx(**env)
+        try:
+            for n, w in [(1 << 13, 3), (1 << 11, 8), (1 << 6, 1)]:
+                check_ntt(c, oracle, edge_matrix(rng, n, w))
+            a = edge_matrix(rng, 1 << 10, 5)
+            check_equal(run_extend(c, a, 1 << 12), oracle.extend_pol(a, 1 << 12), "extend %s" % env)
+        finally:
+            c.close()
+
+
+def test_root_and_reverse_permutation(ctx, oracle, rng):
+    from xlayer_prover_b200 import NTT_Goldilocks
+    g = NTT_Goldilocks(1 << 10, ctx=ctx)
+    for k in range(0, 33):
+        assert g.root(k, 1) == oracle.w(k)
+    a = edge_matrix(rng, 64, 11)
+    dst = np.zeros((64, 4), dtype=np.uint64)
+    g.reversePermutation(dst, a, 64, 5, 4, 11)
+    br = [int(format(i, "06b")[::-1], 2) for i in range(64)]
+    check_equal(dst, a[br, 5:9], "reversePermutation")
+    g2 = NTT_Goldilocks(64, extension=2, ctx=ctx)
+    g2.reversePermutation(dst, a, 64, 5, 4, 11)
+    want = a[br, 5:9].copy()
+    want[[i for i in range(64) if br[i] >= 32]] = 0
+    check_equal(dst, want, "reversePermutation with zero fill")
+    sq = a.copy()
+    g.reversePermutation(sq, sq, 64, 0, 11, 11)
+    check_equal(sq, a[br], "reversePermutation in place")
+
+
+# ---------------------------------------------------------------- extendPol / LDE
+def test_extendpol_kat(ctx, golden):
+    from xlayer_prover_b200 import NTT_Goldilocks
+    ntt = NTT_Goldilocks(16, ctx=ctx)
+    a = np.zeros((32, 8), dtype=np.uint64)
+    a.reshape(-1)[:128] = fib_matrix(16, 8).reshape(-1)
+    ntt.extendPol(a, a, 32, 16, 8, np.zeros((32, 8), dtype=np.uint64))     # output aliases input, tests.cpp:2578
+    check_equal(a[:, 0], golden["extendpol_16x8_to_32_col0"]["out"], "tests.cpp extendePol")
+    check_equal(a[:, 0], golden["lde_block_16x8_to_32_col0"]["out"], "tests.cpp LDE_block")
+
+
+def test_lde_shift49_kat(ctx, golden):
+    from xlayer_prover_b200 import NTT_Goldilocks
+    a = fib_vector(16, 1, 1).reshape(16, 1).copy()
+    NTT_Goldilocks(16, ctx=ctx).INTT(a, a, 16)
+    padded = np.zeros((32, 1), dtype=np.uint64)
+    r = 1
+    for i in range(16):
+        padded[i, 0] = int(a[i, 0]) * r % P
+        r = r * 49 % P
+    NTT_Goldilocks(32, ctx=ctx).NTT(padded, padded, 32)
+    check_equal(padded, golden["lde_16_to_32_shift49"]["out"], "tests.cpp LDE")
+
+
+def test_extendpol_fixtures(ctx, fixtures):
+    for k in ("ext_64x5_b4", "ext_256x3_b2", "ext_32x16_b8", "ext_1x4_b2"):
+        for dev in (False, True):
+            check_equal(run_extend(ctx, fixtures[k + "_in"], fixtures[k + "_out"].shape[0], device=dev), fixtures[k + "_out"], k)
+
+
+@pytest.mark.parametrize("n,c,blow", [(1, 3, 2), (2, 5, 4), (16, 1, 2), (64, 9, 8), (256, 12, 16), (1 << 10, 660, 2),
+                                      (1 << 12, 17, 4), (1 << 13, 8, 2), (1 << 14, 5, 8), (1 << 17, 18, 8)])
+def test_extendpol_vs_oracle(ctx, oracle, port, rng, n, c, blow):
+    a = edge_matrix(rng, n, c)
+    o = port if n * blow == 4 else oracle            # the reference asserts at N_ext = 4 (ntt_goldilocks.cpp:302)
+    want = o.extend_pol(a, n * blow)
+    check_equal(run_extend(ctx, a, n * blow), want, "host")
+    check_equal(run_extend(ctx, a, n * blow, device=True), want, "device")
+    check_equal(run_extend(ctx, a, n * blow, alias=True, device=(n >= 1024)), want, "aliased")
+
+
+def test_config_a_full_parity(ctx, oracle):
+    """BASELINE.json configs[0]: 2^16 rows x 16 cols, blowup 2 -- every extended element and every node."""
+    from xlayer_prover_b200 import synth_matrix
+    a = synth_matrix(1 << 16, 16, 0x9E3779B97F4A7C15 + 1)
+    check_commit(ctx, oracle, a, 1 << 17)
+    check_commit(ctx, oracle, a, 1 << 17, device=True)
+
+
+def test_commit_fixture_and_proofs(ctx, fixtures):
+    from xlayer_prover_b200 import MerkleTreeGL, NTT_Goldilocks
+    a = fixtures["commit_64x9_in"]
+    ext = np.zeros((128, 9), dtype=np.uint64)
+    NTT_Goldilocks(64, ctx=ctx).extendPol(ext, a, 128, 64, 9)
+    check_equal(ext, fixtures["commit_64x9_ext"])
+    mt = MerkleTreeGL(128, 9, ext, ctx=ctx)
+    mt.merkelize()
+    check_equal(mt.nodes, fixtures["commit_64x9_tree"])
+    check_equal(mt.getRoot(), fixtures["commit_64x9_tree"][-4:])
+    assert mt.MerkleProofSize() == 7 and mt.getTreeNumElements() == tree_words(128)
+    proof = np.zeros(9 + 4 * 7, dtype=np.uint64)
+    check_equal(mt.getGroupProof(proof, 77), fixtures["commit_64x9_proof_77"])
+    mt2 = MerkleTreeGL(128, 9, None, ctx=ctx)           # source NULL -> allocated, then copySource (friProve.cpp:120-122)
+    mt2.copySource(ext)
+    mt2.merkelize()
+    check_equal(mt2.nodes, fixtures["commit_64x9_tree"])
+
+
+def test_merkletreegl_vs_reference_class(ctx, reference, rng):
+    from xlayer_prover_b200 import MerkleTreeGL
+    src = edge_matrix(rng, 256, 21)
+    nodes, root, psize, gp = reference.merkle_tree_gl(src)
+    mt = MerkleTreeGL(256, 21, src, ctx=ctx)
+    mt.merkelize()
+    check_equal(mt.nodes, nodes)
+    check_equal(mt.getRoot(), root)
+    assert mt.MerkleProofSize() == psize
+    for idx in (0, 1, 100, 255):
+        check_equal(mt.getGroupProof(np.zeros(21 + 4 * psize, dtype=np.uint64), idx), gp(idx), "proof %d" % idx)
+
+
+def test_commit_streamed_host_path(ctx, oracle, rng):
+    a = edge_matrix(rng, 1 << 12, 37)
+    ctx.set_scratch_limit(((1 << 13) + (1 << 12)) * 8 * 8 * 2)      # 8-column blocks -> 5 streamed blocks
+    try:
+        check_commit(ctx, oracle, a, 1 << 13)
+        check_commit(ctx, oracle, a, 1 << 13, device=True)
+    finally:
+        ctx.set_scratch_limit(0)
+    # pinned host buffers (what bench.py's e2e leg uses)
+    n, c, ne = 1 << 12, 37, 1 << 13
+    hin = ctx.host_alloc(n * c * 8)
+    hext = ctx.host_alloc(ne * c * 8)
+    ctx.memcpy(hin, a, a.nbytes)
+    tree = np.zeros(tree_words(ne), dtype=np.uint64)
+    root = ctx.commit(hext, tree, hin, n, ne, c)
+    ext = np.zeros((ne, c), dtype=np.uint64)
+    ctx.memcpy(ext, hext, ext.nbytes)
+    want = oracle.extend_pol(a, ne)
+    check_equal(ext, want, "pinned ext")
+    check_equal(tree, oracle.merkletree(want), "pinned tree")
+    check_equal(root, tree[-4:])
+    ctx.host_free(hin)
+    ctx.host_free(hext)
+
+
+def test_argument_errors(ctx):
+    from xlayer_prover_b200 import GLP_E_ARG, GLP_E_DOMAIN, GlpError, NTT_Goldilocks
+    a = np.zeros((12, 2), dtype=np.uint64)
+    with pytest.raises(GlpError) as e:
+        ctx.ntt(a, a, 12, 2)
+    assert e.value.code == GLP_E_ARG
+    with pytest.raises(GlpError) as e:
+        ctx.ntt(a, a, 1 << 33, 1)
+    assert e.value.code == GLP_E_DOMAIN
+    with pytest.raises(ValueError):
+        NTT_Goldilocks(1 << 33)                         # std::range_error in the reference
+    with pytest.raises(GlpError):
+        ctx.merkletree(np.zeros(100, dtype=np.uint64), a, 2, 12)
+    ctx.merkletree(a, a, 2, 0)                          # num_rows == 0 returns (poseidon_goldilocks.cpp:268-271)
+
+
+# ---------------------------------------------------------------- size-independent properties at large sizes
+def test_large_roundtrip_and_linearity(ctx):
+    """2^22 x 16 on the device: INTT(NTT(x)) == x (checksum of every word), and LDE(a+b) == LDE(a)+LDE(b)."""
+    n, c = 1 << 22, 16
+    words = n * c
+    x = ctx.device_alloc(words * 8)
+    y = ctx.device_alloc(words * 8)
+    ctx.synth_fill(x, n, c, 77)
+    before = ctx.checksum(x, words)
+    ctx.ntt(y, x, n, c)
+    assert ctx.checksum(y, words) != before
+    ctx.ntt(y, y, n, c, inverse=True)
+    assert ctx.checksum(y, words) == before
+    ctx.device_free(y)
+    ctx.device_free(x)
+    n, c, ne = 1 << 20, 8, 1 << 21
+    bufs = [ctx.device_alloc(n * c * 8) for _ in range(2)]
+    outs = [ctx.device_alloc(ne * c * 8) for _ in range(2)]
+    ctx.synth_fill(bufs[0], n, c, 1)
+    ctx.synth_fill(bufs[1], n, c, 2)
+    sums = []
+    for i in range(2):
+        ctx.extend_pol(outs[i], bufs[i], ne, n, c)
+        sums.append(ctx.checksum(outs[i], ne * c))
+    a = ctx.to_host(bufs[0], (n, c)).astype(object) + ctx.to_host(bufs[1], (n, c)).astype(object)
+    ctx.memcpy(bufs[0], (a % P).astype(np.uint64), n * c * 8)
+    ctx.extend_pol(outs[0], bufs[0], ne, n, c)
+    s = ctx.checksum(outs[0], ne * c)
+    assert s == ((sums[0][0] + sums[1][0]) % P, (sums[0][1] + sums[1][1]) % P)
+    for p in bufs + outs:
+        ctx.device_free(p)
+
+
+def test_large_lde_of_monomials(ctx, oracle):
+    """Closed form at 2^20 -> 2^21: a column holding x^d on the subgroup extends to (shift*w_ext^i)^d."""
+    n, ne = 1 << 20, 1 << 21
+    degrees = [0, 1, 2, 12345, n - 1]
+    a = monomial_columns(n, degrees, oracle.w(20))
+    ext = run_extend(ctx, a, ne, device=True)
+    wext = oracle.w(21)
+    rows = [0, 1, 2, 3, ne // 2, ne - 1] + [int(r) for r in np.random.default_rng(3).integers(0, ne, size=200)]
+    for i in rows:
+        pt = 7 * pow(wext, i, P) % P
+        for c, d in enumerate(degrees):
+            assert int(ext[i, c]) == pow(pt, d, P), (i, d)
+
+
+def test_large_merkle_paths(ctx, oracle):
+    """2^20 leaves x 64 columns: recompute sampled leaves with the oracle and walk their paths to the root."""
+    n, c = 1 << 20, 64
+    src = ctx.device_alloc(n * c * 8)
+    tree = ctx.device_alloc(tree_words(n) * 8)
+    ctx.synth_fill(src, n, c, 99)
+    ctx.merkletree(tree, src, c, n)
+    nodes = ctx.to_host(tree, (tree_words(n),))
+    from xlayer_prover_b200 import synth_matrix
+    for idx in [0, 1, n - 1] + [int(r) for r in np.random.default_rng(4).integers(0, n, size=20)]:
+        row = synth_matrix(1, c, 99, row0=idx, ncols_total=c)[0]
+        proof = np.zeros(c + 4 * 20, dtype=np.uint64)
+        ctx.merkle_group_proof(proof, src, tree, c, n, idx)
+        check_equal(proof[:c], row)
+        h = oracle.linear_hash(row)
+        check_equal(nodes[4 * idx: 4 * idx + 4], h, "leaf %d" % idx)
+        i = idx
+        for lvl in range(20):
+            sib = proof[c + 4 * lvl: c + 4 * lvl + 4]
+            pair = np.concatenate([h, sib] if i % 2 == 0 else [sib, h] + [])
+            h = oracle.hash_full_result(np.concatenate([pair, np.zeros(4, dtype=np.uint64)]))[:4]
+            i //= 2
+        check_equal(h, nodes[-4:], "root from leaf %d" % idx)
+    ctx.device_free(src)
+    ctx.device_free(tree)

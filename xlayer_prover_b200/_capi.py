@@ -48,6 +48,9 @@ SIGNATURES = {
     "glp_synth_fill": (i32, [vp, vp, u64, u64, u64, u64, u64, u64]),
     "glp_checksum": (i32, [vp, vp, u64, u64p]),
     "glp_field_selftest": (i32, [vp, vp, vp, u64, vp]),
+    "glp_set_profiling": (i32, [vp, i32]),
+    "glp_get_profile": (i32, [vp, C.POINTER(C.c_float), C.POINTER(u32)]),
+    "glp_measure_int_peak": (i32, [vp, C.POINTER(C.c_double)]),
 }
 
 
@@ -213,6 +216,21 @@ class Context:
         out = np.zeros((a.size, 5), dtype=np.uint64)
         self.lib.check(self.lib.glp_field_selftest(self.h, ptr_of(a), ptr_of(b), a.size, ptr_of(out)))
         return out
+
+
+    def set_profiling(self, on): self.lib.check(self.lib.glp_set_profiling(self.h, int(on)))
+
+    def get_profile(self):
+        """{stage: (ms, intervals)} accumulated since the last call; synchronises the stream."""
+        ms, cnt = (C.c_float * 4)(), (u32 * 4)()
+        self.lib.check(self.lib.glp_get_profile(self.h, ms, cnt))
+        names = ("intt", "ntt_ext", "leaf_hash", "tree_levels")
+        return {n: (float(ms[i]), int(cnt[i])) for i, n in enumerate(names)}
+
+    def measure_int_peak(self):
+        out = (C.c_double * 3)()
+        self.lib.check(self.lib.glp_measure_int_peak(self.h, out))
+        return {"imad_lane_ops_per_s": out[0], "iadd3_lane_ops_per_s": out[1], "interleaved_lane_ops_per_s": out[2]}
 
 
 def tree_num_elements(nrows):

@@ -90,3 +90,36 @@ __global__ void k_field_selftest(const gl_t *a, const gl_t *b, uint64_t n, gl_t 
     out[5 * i + 3] = gl_canon(gl_mul_pow2(x, (unsigned)(y % 96)));
     out[5 * i + 4] = gl_canon(x);
 }
+
+// ---- integer-pipe peak micro-benchmarks ("the IMAD peak must be measured on the box") ----
+// mode 0: 8 independent IMAD (32-bit multiply-add, same pipe as IMAD.WIDE) chains per thread; mode 1: 8 independent IADD3 chains; mode 2: both interleaved.
+// Each loop iteration issues 8 (mode 0/1) or 16 (mode 2) dependent-free integer instructions per thread.
+__global__ void k_int_peak(uint64_t *sink, uint32_t iters, int mode)
+{
+    uint32_t a = threadIdx.x * 2654435761u + 12345u, b = (blockIdx.x * 40503u + 977u) ^ (threadIdx.x * 97u);
+    uint32_t m0 = a, m1 = b, m2 = a ^ b, m3 = a + b, m4 = a * 3u, m5 = b * 5u, m6 = a * 7u, m7 = b * 11u;
+    uint32_t s0 = a, s1 = b, s2 = a ^ 1u, s3 = b ^ 2u, s4 = a ^ 3u, s5 = b ^ 4u, s6 = a ^ 5u, s7 = b ^ 6u;
+    // every operand is loop-carried, so ptxas can neither hoist the product nor fold the adds
+#if GL_DEVICE_PTX
+#define GLP_MADW(acc, y) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(acc) : "r"(y), "r"(a))
+#define GLP_ADD3(acc, x, y) asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(acc) : "r"(x), "r"(y))
+#else
+#define GLP_MADW(acc, y) acc = acc * (y) + a
+#define GLP_ADD3(acc, x, y) acc += (x) + (y)
+#endif
+    for (uint32_t i = 0; i < iters; i++) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            if (mode != 1) {
+                GLP_MADW(m0, b); GLP_MADW(m1, b); GLP_MADW(m2, b); GLP_MADW(m3, b);
+                GLP_MADW(m4, b); GLP_MADW(m5, b); GLP_MADW(m6, b); GLP_MADW(m7, b);
+            }
+            if (mode != 0) {
+                GLP_ADD3(s0, s4, s5); GLP_ADD3(s1, s5, s6); GLP_ADD3(s2, s6, s7); GLP_ADD3(s3, s7, s4);
+                GLP_ADD3(s4, s0, s1); GLP_ADD3(s5, s1, s2); GLP_ADD3(s6, s2, s3); GLP_ADD3(s7, s3, s0);
+            }
+        }
+    }
+    uint32_t r = m0 ^ m1 ^ m2 ^ m3 ^ m4 ^ m5 ^ m6 ^ m7 ^ s0 ^ s1 ^ s2 ^ s3 ^ s4 ^ s5 ^ s6 ^ s7;
+    if (r == iters * 0x9E3779B1u + 7u) sink[0] = r;   // practically never true; keeps the chains alive
+}

@@ -64,6 +64,29 @@ struct glp_ctx {
     DevBuf ext, nodes, tmp_in, tmp_out;      // commit / staging
     DevBuf partial;                          // checksum partials
     std::vector<void *> tables;              // everything to free
+    bool profiling = false;
+    struct ProfSpan { int kind; cudaEvent_t a, b; };
+    std::vector<ProfSpan> spans;
+};
+
+// bracket a stage with events when profiling is on
+struct ProfScope {
+    glp_ctx *ctx;
+    cudaEvent_t a = nullptr, b = nullptr;
+    int kind;
+    ProfScope(glp_ctx *c, int k) : ctx(c), kind(k)
+    {
+        if (!ctx->profiling) return;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, ctx->stream);
+    }
+    ~ProfScope()
+    {
+        if (!a) return;
+        cudaEventRecord(b, ctx->stream);
+        ctx->spans.push_back({kind, a, b});
+    }
 };
 
 static int ensure(glp_ctx *ctx, DevBuf &b, size_t bytes)
@@ -424,9 +447,15 @@ static int dev_extend_pol(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_
     for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
         const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
         // coefficients * shift^j / N  (INTT with extend, ntt_goldilocks.cpp:345)
-        GLP(run_transform(ctx, logN, in, in_pitch, c0, s2, w, 0, w, n, true, true, s1));
+        {
+            ProfScope ps(ctx, 0);
+            GLP(run_transform(ctx, logN, in, in_pitch, c0, s2, w, 0, w, n, true, true, s1));
+        }
         // zero-padded forward transform of size n_ext (ntt_goldilocks.cpp:346)
-        GLP(run_transform(ctx, logE, s2, w, 0, out, out_pitch, c0, w, n, false, false, s1));
+        {
+            ProfScope ps(ctx, 1);
+            GLP(run_transform(ctx, logE, s2, w, 0, out, out_pitch, c0, w, n, false, false, s1));
+        }
     }
     return GLP_OK;
 }
@@ -568,8 +597,14 @@ static int dev_tree_levels(glp_ctx *ctx, gl_t *level, uint64_t n)
 }
 static int dev_merkletree(glp_ctx *ctx, gl_t *tree, const gl_t *in, uint64_t width, uint64_t pitch, uint64_t nrows)
 {
-    GLP(dev_leaf_hash(ctx, tree, in, width, pitch, nrows));
-    GLP(dev_tree_levels(ctx, tree, nrows));
+    {
+        ProfScope ps(ctx, 2);
+        GLP(dev_leaf_hash(ctx, tree, in, width, pitch, nrows));
+    }
+    {
+        ProfScope ps(ctx, 3);
+        GLP(dev_tree_levels(ctx, tree, nrows));
+    }
     return GLP_OK;
 }
 
@@ -734,9 +769,15 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
             GLP(ensure(ctx, ctx->s1, (size_t)n_ext * wb * sizeof(gl_t)));
             GLP(ensure(ctx, ctx->s2, (size_t)n * wb * sizeof(gl_t)));
             const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
-            GLP(run_transform(ctx, logN, stage[k & 1], w, 0, (gl_t *)ctx->s2.p, w, 0, w, n, true, true, (gl_t *)ctx->s1.p));
+            {
+                ProfScope ps(ctx, 0);
+                GLP(run_transform(ctx, logN, stage[k & 1], w, 0, (gl_t *)ctx->s2.p, w, 0, w, n, true, true, (gl_t *)ctx->s1.p));
+            }
             CU(cudaEventRecord(free_stage[k], ctx->stream));
-            GLP(run_transform(ctx, logE, (gl_t *)ctx->s2.p, w, 0, dext, ncols, c0, w, n, false, false, (gl_t *)ctx->s1.p));
+            {
+                ProfScope ps(ctx, 1);
+                GLP(run_transform(ctx, logE, (gl_t *)ctx->s2.p, w, 0, dext, ncols, c0, w, n, false, false, (gl_t *)ctx->s1.p));
+            }
             CU(cudaEventRecord(done[k], ctx->stream));
             if (out_ext && !ext_dev) {
                 CU(cudaStreamWaitEvent(ctx->copy_stream[1], done[k], 0));
@@ -824,4 +865,54 @@ extern "C" int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_
     }
     release(da); release(db); release(dout);
     return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// measurement hooks
+// ------------------------------------------------------------------------------------------------
+extern "C" int glp_set_profiling(glp_ctx *ctx, int on)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    ctx->profiling = on != 0;
+    return GLP_OK;
+}
+extern "C" int glp_get_profile(glp_ctx *ctx, float ms[4], uint32_t count[4])
+{
+    if (!ctx || !ms || !count) return fail(GLP_E_ARG, "glp_get_profile: NULL argument");
+    for (int i = 0; i < 4; i++) { ms[i] = 0; count[i] = 0; }
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (auto &sp : ctx->spans) {
+        float t = 0;
+        if (cudaEventElapsedTime(&t, sp.a, sp.b) == cudaSuccess && sp.kind >= 0 && sp.kind < 4) { ms[sp.kind] += t; count[sp.kind]++; }
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    ctx->spans.clear();
+    cudaGetLastError();
+    return GLP_OK;
+}
+extern "C" int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3])
+{
+    if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_int_peak: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    GLP(ensure(ctx, ctx->partial, 2 * 148 * 8 * sizeof(gl_t)));
+    cudaEvent_t a, b;
+    CU(cudaEventCreate(&a));
+    CU(cudaEventCreate(&b));
+    const unsigned grid = 148 * 8, block = 256;
+    const uint32_t iters = 4096;
+    for (int mode = 0; mode < 3; mode++) {
+        LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, 64u, mode);      // warm-up
+        CU(cudaEventRecord(a, ctx->stream));
+        LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, iters, mode);
+        CU(cudaEventRecord(b, ctx->stream));
+        CU(cudaEventSynchronize(b));
+        float t = 0;
+        CU(cudaEventElapsedTime(&t, a, b));
+        const double per_thread = (double)iters * 8 * 8 * (mode == 2 ? 2 : 1);
+        ops_per_s[mode] = per_thread * grid * block / (t * 1e-3);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    return GLP_OK;
 }

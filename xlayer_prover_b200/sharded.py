@@ -1,0 +1,127 @@
+"""Multi-GPU commit: column-sharded LDE -> all-to-all over NVLink -> row-sharded Merkle subtrees -> top levels on rank 0.
+
+One process per GPU (torch.distributed; NCCL on the B200 box, gloo in the CPU tests).  The path shards
+exactly as BASELINE.json's north_star prescribes:
+
+  1. columns are independent polynomials: rank g extends its own column slice [c_g, c_{g+1}) with
+     glp_extend_pol_pitched (boundaries are multiples of 8, so every 8-wide sponge block has one owner);
+  2. ONE exchange step: rank g sends rows [j*R, (j+1)*R) (R = N_ext/G) of its slice to rank j
+     (all_to_all_single), and each rank interleaves what it received into a reference-layout
+     [R x C] row slab of the extended matrix;
+  3. rank j hashes its R leaf rows and builds its subtree (glp_merkletree on the slab);
+  4. the G subtrees are gathered on rank 0, re-laid level-major into the reference's `nodes` layout
+     (poseidon_goldilocks.cpp:283-300) and the top log2(G) levels are hashed there (glp_merkle_levels).
+
+torch is plumbing only: it owns the buffers, the NCCL communicator and the current stream; all arithmetic
+is in libglprover.so.  Results are identical for every G (tests/test_sharded.py).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from ._capi import tree_num_elements
+
+
+def column_bounds(ncols, world):
+    """c_0..c_G with every boundary a multiple of 8 (except the last, = ncols)."""
+    nblk = (ncols + 7) // 8
+    return [min(ncols, 8 * ((g * nblk) // world)) for g in range(world)] + [ncols]
+
+
+def assemble_tree(subtrees, n_ext, world):
+    """Re-lay G row-sharded subtrees (each (2R-1)*4 words, level-major) into the first
+    levels of the full level-major tree; returns (full_tree, offset_of_level_with_G_nodes)."""
+    R = n_ext // world
+    full = torch.zeros(tree_num_elements(n_ext), dtype=torch.int64, device=subtrees[0].device)
+    off_full, off_sub, n_full, n_sub = 0, 0, n_ext, R
+    while n_sub >= 1:
+        for g, t in enumerate(subtrees):
+            full[off_full + 4 * g * n_sub: off_full + 4 * (g + 1) * n_sub] = t[off_sub: off_sub + 4 * n_sub]
+        if n_sub == 1:
+            break
+        off_full += 4 * n_full
+        off_sub += 4 * n_sub
+        n_full //= 2
+        n_sub //= 2
+    return full, off_full
+
+
+class ShardedCommit:
+    """commit(in_slice) for one rank.  `ctx` is this rank's glprover Context; `device` the torch device the
+    buffers live on ('cuda:N', or 'cpu' with the emulator backend in the gloo tests)."""
+
+    def __init__(self, ctx, n, n_ext, ncols, group=None, device=None):
+        self.ctx, self.n, self.n_ext, self.ncols = ctx, n, n_ext, ncols
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        assert n_ext % self.world == 0 and (self.world & (self.world - 1)) == 0, "world size must be a power of two dividing n_ext"
+        self.device = torch.device(device if device is not None else "cuda:%d" % ctx.device)
+        self.bounds = column_bounds(ncols, self.world)
+        self.c0, self.c1 = self.bounds[self.rank], self.bounds[self.rank + 1]
+        self.w = self.c1 - self.c0
+        self.R = n_ext // self.world
+        i64 = dict(dtype=torch.int64, device=self.device)
+        # buffer A holds my columns for all rows (LDE output), then -- after the exchange -- my rows for all
+        # columns (the slab the Merkle stage reads); buffer B receives the all-to-all.  Peak = A + B.
+        self.buf_a = torch.empty(max(1, n_ext * self.w, self.R * ncols), **i64)
+        self.ext_cols = self.buf_a[: max(1, n_ext * self.w)]
+        self.slab = self.buf_a[: self.R * ncols]
+        self.recv = torch.empty(self.R * ncols, **i64) if self.world > 1 else None
+        self.subtree = torch.empty(tree_num_elements(self.R), **i64)
+        self.tree = None
+
+    def bind_stream(self):
+        """Launch the library's kernels on torch's current stream so they order with the collectives."""
+        if self.device.type == "cuda":
+            self.ctx.set_stream(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def extend(self, in_slice, in_pitch=None):
+        """Step 1: LDE of my column slice.  in_slice: [n x w] (pitch in_pitch, default dense)."""
+        if self.w:
+            self.ctx.extend_pol_pitched(self.ext_cols, self.w, in_slice, in_pitch or self.w, self.n_ext, self.n, self.w)
+
+    def exchange(self):
+        """Step 2: the one collective, then interleave into the row slab."""
+        R, C, G = self.R, self.ncols, self.world
+        if G == 1:
+            return                              # slab and ext_cols are the same memory
+        in_splits = [R * self.w] * G
+        out_splits = [R * (self.bounds[s + 1] - self.bounds[s]) for s in range(G)]
+        dist.all_to_all_single(self.recv, self.ext_cols[: self.n_ext * self.w], out_splits, in_splits, group=self.group)
+        slab2d = self.slab.view(R, C)
+        off = 0
+        for s in range(G):
+            ws = self.bounds[s + 1] - self.bounds[s]
+            if ws:
+                slab2d[:, self.bounds[s]: self.bounds[s + 1]].copy_(self.recv[off: off + R * ws].view(R, ws))
+            off += R * ws
+
+    def merkle(self):
+        """Step 3: my subtree."""
+        self.ctx.merkletree(self.subtree, self.slab, self.ncols, self.R, 1)
+
+    def finish(self):
+        """Step 4: gather subtrees on rank 0, assemble, hash the top log2(G) levels.  Returns root on rank 0."""
+        G = self.world
+        if G == 1:
+            self.tree = self.subtree
+            return self.tree[-4:].clone()
+        gathered = [torch.empty_like(self.subtree) for _ in range(G)] if self.rank == 0 else None
+        dist.gather(self.subtree, gathered, dst=0, group=self.group)
+        if self.rank != 0:
+            return None
+        self.tree, off_top = assemble_tree(gathered, self.n_ext, G)
+        self.ctx.merkle_levels(self.tree[off_top:], G)
+        return self.tree[-4:].clone()
+
+    def commit(self, in_slice, in_pitch=None):
+        self.bind_stream()
+        self.extend(in_slice, in_pitch)
+        self.exchange()
+        self.merkle()
+        return self.finish()
+
+
+def to_numpy_u64(t):
+    return t.detach().cpu().numpy().view(np.uint64)
