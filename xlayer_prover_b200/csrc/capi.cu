@@ -575,9 +575,9 @@ static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncol
 {
     if (!nrows) return GLP_OK;
     const int vec16 = (pitch % 2 == 0) && (((uintptr_t)in) % 16 == 0);
-    const uint64_t nblk = (nrows + POS_BLOCK - 1) / POS_BLOCK;
+    const uint64_t nblk = (nrows + POS_LEAF_BLOCK - 1) / POS_LEAF_BLOCK;
     if (nblk > 0x7FFFFFFFull) return fail(GLP_E_ARG, "too many rows");
-    LAUNCH_FLAT(ctx, k_linear_hash_rows, (unsigned)nblk, POS_BLOCK, out4, in, ncols, pitch, nrows, vec16);
+    LAUNCH_FLAT(ctx, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>, (unsigned)nblk, POS_LEAF_BLOCK, out4, in, ncols, pitch, nrows, vec16);
     CU(cudaGetLastError());
     return GLP_OK;
 }

@@ -53,11 +53,13 @@ GL_HD gl_t gl_add(gl_t a, gl_t b)
         "add.cc.u32 a0, a0, b0;\n\t"
         "addc.cc.u32 a1, a1, b1;\n\t"
         "addc.u32 m, 0, 0;\n\t"                 // carry
-        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"   // + carry*EPS
-        "madc.hi.cc.u32 a1, m, 0xffffffff, a1;\n\t"
+        "sub.u32 m, 0, m;\n\t"                  // 0xffffffff on carry.  (A mad by 0xffffffff would do this on the fma pipe,
+        "add.cc.u32 a0, a0, m;\n\t"             //  6 cycles of it; and `subc` straight after an add chain reads the carry
+        "addc.cc.u32 a1, a1, 0;\n\t"            //  flag with the wrong polarity.)
         "addc.u32 m, 0, 0;\n\t"                 // second wrap (only when both operands >= p-ish)
-        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"
-        "madc.hi.u32 a1, m, 0xffffffff, a1;\n\t"
+        "sub.cc.u32 a0, a0, m;\n\t"
+        "subc.u32 a1, a1, 0;\n\t"
+        "add.u32 a1, a1, m;\n\t"
         "mov.b64 %0, {a0,a1};\n\t"
         "}" : "=l"(r) : "l"(a), "l"(b));
     return r;
@@ -80,8 +82,9 @@ GL_HD gl_t gl_add_c(gl_t a, gl_t b)
         "add.cc.u32 a0, a0, b0;\n\t"
         "addc.cc.u32 a1, a1, b1;\n\t"
         "addc.u32 m, 0, 0;\n\t"
-        "mad.lo.cc.u32 a0, m, 0xffffffff, a0;\n\t"
-        "madc.hi.u32 a1, m, 0xffffffff, a1;\n\t"
+        "sub.cc.u32 a0, a0, m;\n\t"
+        "subc.u32 a1, a1, 0;\n\t"
+        "add.u32 a1, a1, m;\n\t"
         "mov.b64 %0, {a0,a1};\n\t"
         "}" : "=l"(r) : "l"(a), "l"(b));
     return r;
@@ -135,11 +138,12 @@ GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi)
         "subc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 p0, p0, m;\n\t"             //   - EPS on borrow
         "subc.u32 p1, p1, 0;\n\t"
-        "mad.lo.cc.u32 p0, p2, 0xffffffff, p0;\n\t"  // + p2*EPS        [2^64 = EPS]
+        "mad.lo.cc.u32 p0, p2, 0xffffffff, p0;\n\t"  // + p2*EPS        [2^64 = EPS]   (one IMAD.WIDE)
         "madc.hi.cc.u32 p1, p2, 0xffffffff, p1;\n\t"
-        "addc.u32 m, 0, 0;\n\t"
-        "mad.lo.cc.u32 p0, m, 0xffffffff, p0;\n\t"   //   + EPS on carry
-        "madc.hi.u32 p1, m, 0xffffffff, p1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"                      // + carry*EPS = - carry + (carry << 32)
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        "add.u32 p1, p1, m;\n\t"
         "mov.b64 %0, {p0,p1};\n\t"
         "}" : "=l"(r) : "l"(lo), "l"(hi));
     return r;

@@ -25,6 +25,8 @@
 GLP_CONSTANT gl_t POS_RC[GLP_POSEIDON_RC_N] = {GLP_POSEIDON_RC_INIT};
 GLP_CONSTANT gl_t POS_PRE[144] = {GLP_POSEIDON_PRE_INIT};
 GLP_CONSTANT gl_t POS_SP[GLP_POSEIDON_SP_N] = {GLP_POSEIDON_SP_INIT};
+GLP_CONSTANT gl_t POS_RCF[96] = {GLP_POSEIDON_RCF_INIT};     // full-round constants, one row of 12 per round
+GLP_CONSTANT gl_t POS_PRET[144] = {GLP_POSEIDON_PRET_INIT};  // pre-matrix, transposed: row i = weights of output i
 
 #define POS_WIDTH 12
 #define POS_RATE 8
@@ -120,8 +122,9 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
         "mad.lo.cc.u32 l0, h1, 0xffffffff, l0;\n\t"
         "madc.hi.cc.u32 l1, h1, 0xffffffff, l1;\n\t"
         "addc.u32 m, 0, 0;\n\t"
-        "mad.lo.cc.u32 l0, m, 0xffffffff, l0;\n\t"
-        "madc.hi.u32 l1, m, 0xffffffff, l1;\n\t"
+        "sub.cc.u32 l0, l0, m;\n\t"
+        "subc.u32 l1, l1, 0;\n\t"
+        "add.u32 l1, l1, m;\n\t"
         "mov.b64 %0, {l0,l1};\n\t"
         "}" : "=l"(r) : "l"(L), "l"(H));
     return r;
@@ -129,6 +132,20 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
     uint64_t lo = L + (H << 32);
     uint64_t top = (H >> 32) + (lo < L);
     return gl_reduce128(lo, top);
+#endif
+}
+
+// acc(64) += a(32) * c(32): written as a carry-chain pair so that ptxas keeps ONE IMAD.WIDE with the 64-bit
+// addend (a plain `L += (uint64_t)a * c` is strength-reduced to shifts/adds for small c and its accumulate
+// split into IADD3 + IADD3.X, which moves the work onto the ALU pipe)
+GL_HD void pos_macw(uint32_t &l0, uint32_t &l1, uint32_t a, uint32_t c)
+{
+#if GL_DEVICE_PTX
+    asm("mad.lo.cc.u32 %0, %2, %3, %0;\n\tmadc.hi.u32 %1, %2, %3, %1;" : "+r"(l0), "+r"(l1) : "r"(a), "r"(c));
+#else
+    uint64_t t = (((uint64_t)l1 << 32) | l0) + (uint64_t)a * c;
+    l0 = (uint32_t)t;
+    l1 = (uint32_t)(t >> 32);
 #endif
 }
 
@@ -140,66 +157,128 @@ GL_HD void pos_mds(gl_t x[12])
     for (int j = 0; j < 12; j++) { lo[j] = (uint32_t)x[j]; hi[j] = (uint32_t)(x[j] >> 32); }
 #pragma unroll
     for (int i = 0; i < 12; i++) {
-        uint64_t L = 0, H = 0;
+        uint32_t L0 = 0, L1 = 0, H0 = 0, H1 = 0;
 #pragma unroll
         for (int j = 0; j < 12; j++) {
-            uint32_t c = circ[(j - i + 12) % 12] + ((i == 0 && j == 0) ? GLP_MDS_DIAG0 : 0);
-            L += (uint64_t)lo[j] * c;
-            H += (uint64_t)hi[j] * c;
+            const uint32_t c = circ[(j - i + 12) % 12] + ((i == 0 && j == 0) ? GLP_MDS_DIAG0 : 0);
+            pos_macw(L0, L1, lo[j], c);
+            pos_macw(H0, H1, hi[j], c);
         }
-        x[i] = pos_mds_fold(L, H);
+        x[i] = pos_mds_fold(((uint64_t)L1 << 32) | L0, ((uint64_t)H1 << 32) | H0);
     }
 }
 
 // ---- the permutation ----
-GL_HD void pos_permute(gl_t x[12])
+// Code layout matters as much as the arithmetic here: a fully unrolled permutation is ~125 KB of SASS, four
+// times the instruction cache, and with 16 warps of an SM at 16 different places in it the kernel stalls on
+// instruction fetch (ncu: stall_no_instruction 6 of 11 cycles per issue).  So the eight full rounds are ONE
+// loop body (S-box group + MDS), the dense pre-matrix is a 12-trip loop that shifts its results through a
+// register queue, and the 22 partial rounds are a loop: ~25 KB of hot code.  POS_LOCKSTEP additionally
+// makes the warps of a CTA meet at a barrier every round so that they fetch the same lines together.
+#ifndef POS_SBOX_GROUP
+#define POS_SBOX_GROUP 12         // S-boxes per trip of the S-box loop (12 = unrolled; 4 or 6 = rolled with a rotating state: smaller code, measured 2-5 % slower)
+#endif
+#ifndef POS_ROLL_PRE
+#define POS_ROLL_PRE 0            // 1 = 12-trip pre-matrix loop with a register queue (3 KB instead of 30 KB of code, measured 1-2 % slower)
+#endif
+
+template <bool LOCKSTEP>
+GL_HD void pos_round_sync()
+{
+#if GL_DEVICE_PTX
+    if (LOCKSTEP) __syncthreads();
+#endif
+}
+
+// x_i = x_i^7 + rc_i for all 12, as 12/G trips over G lanes with the state rotated by G after each trip
+GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc)
+{
+    constexpr int G = POS_SBOX_GROUP;
+    static_assert(12 % G == 0, "POS_SBOX_GROUP must divide 12");
+    if (G == 12) {
+#pragma unroll
+        for (int i = 0; i < 12; i++) x[i] = gl_add_c(gl_pow7(x[i]), rc[i]);
+        return;
+    }
+#pragma unroll 1
+    for (int q = 0; q < 12 / G; q++) {
+        gl_t t[G];
+#pragma unroll
+        for (int i = 0; i < G; i++) t[i] = gl_add_c(gl_pow7(x[i]), rc[q * G + i]);
+#pragma unroll
+        for (int i = 0; i + G < 12; i++) x[i] = x[i + G];
+#pragma unroll
+        for (int i = 0; i < G; i++) x[12 - G + i] = t[i];
+    }
+}
+
+// x <- PRE^T x  (the dense pre-multiplied matrix before the partial rounds)
+GL_HD void pos_pre_layer(gl_t x[12])
+{
+#if POS_ROLL_PRE
+    gl_t out[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) out[i] = 0;
+#pragma unroll 1
+    for (int i = 0; i < 12; i++) {
+        const gl_t *col = POS_PRET + 12 * i;
+        GlDotAcc acc;
+        gl_dot_init(acc);
+#pragma unroll
+        for (int j = 0; j < 12; j++) gl_dot_mac(acc, x[j], col[j]);
+#pragma unroll
+        for (int k = 0; k < 11; k++) out[k] = out[k + 1];
+        out[11] = gl_dot_fold(acc);
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++) x[i] = out[i];
+#else
+    gl_t y[12];
+#pragma unroll
+    for (int i = 0; i < 12; i++) y[i] = x[i];
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        GlDotAcc acc;
+        gl_dot_init(acc);
+#pragma unroll
+        for (int j = 0; j < 12; j++) gl_dot_mac(acc, y[j], POS_PRE[j * 12 + i]);
+        x[i] = gl_dot_fold(acc);
+    }
+#endif
+}
+
+template <bool LOCKSTEP>
+GL_HD void pos_permute_t(gl_t x[12])
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = gl_add_c(x[i], POS_RC[i]);
 
-    // first half: 3 x {pow7 + C, MDS}, then pow7 + C and the dense pre-multiplied matrix
+    // 8 full rounds {x^7 + C ; linear layer}; the linear layer of round 3 is the pre-matrix followed by the
+    // 22 partial rounds, every other one is the MDS matrix; round 7 adds zero constants
 #pragma unroll 1
-    for (int r = 0; r < 3; r++) {
+    for (int r = 0; r < 8; r++) {
+        pos_round_sync<LOCKSTEP>();
+        pos_sbox_layer(x, POS_RCF + 12 * r);
+        if (r != 3) {
+            pos_mds(x);
+        } else {
+            pos_pre_layer(x);
+            // partial rounds: x0 = x0^7 + C;  s0 = <x, S[0..12)>;  x_i += x0 * S[11+i] (i >= 1);  x0 = s0
+#pragma unroll 1
+            for (int p = 0; p < 22; p++) {
+                pos_round_sync<LOCKSTEP>();
+                const gl_t *S = POS_SP + 23 * p;
+                x[0] = gl_add_c(gl_pow7(x[0]), POS_RC[60 + p]);
+                GlDotAcc acc;
+                gl_dot_init(acc);
 #pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = gl_add_c(gl_pow7(x[i]), POS_RC[12 * (r + 1) + i]);
-        pos_mds(x);
-    }
-    {
-        gl_t y[12];
+                for (int i = 0; i < 12; i++) gl_dot_mac(acc, x[i], S[i]);
 #pragma unroll
-        for (int i = 0; i < 12; i++) y[i] = gl_add_c(gl_pow7(x[i]), POS_RC[48 + i]);
-#pragma unroll
-        for (int i = 0; i < 12; i++) {
-            GlDotAcc acc;
-            gl_dot_init(acc);
-#pragma unroll
-            for (int j = 0; j < 12; j++) gl_dot_mac(acc, y[j], POS_PRE[j * 12 + i]);
-            x[i] = gl_dot_fold(acc);
+                for (int i = 1; i < 12; i++) x[i] = gl_mul_add(x[0], S[11 + i], x[i]);
+                x[0] = gl_dot_fold(acc);
+            }
         }
     }
-
-    // 22 partial rounds: x0 = x0^7 + C;  s0 = <x, S[0..12)>;  x_i += x0 * S[11+i] (i >= 1);  x0 = s0
-#pragma unroll 1
-    for (int r = 0; r < 22; r++) {
-        const gl_t *S = POS_SP + 23 * r;
-        x[0] = gl_add_c(gl_pow7(x[0]), POS_RC[60 + r]);
-        GlDotAcc acc;
-        gl_dot_init(acc);
-#pragma unroll
-        for (int i = 0; i < 12; i++) gl_dot_mac(acc, x[i], S[i]);
-#pragma unroll
-        for (int i = 1; i < 12; i++) x[i] = gl_mul_add(x[0], S[11 + i], x[i]);
-        x[0] = gl_dot_fold(acc);
-    }
-
-    // second half: 3 x {pow7 + C, MDS}, then pow7 and MDS
-#pragma unroll 1
-    for (int r = 0; r < 3; r++) {
-#pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = gl_add_c(gl_pow7(x[i]), POS_RC[82 + 12 * r + i]);
-        pos_mds(x);
-    }
-#pragma unroll
-    for (int i = 0; i < 12; i++) x[i] = gl_pow7(x[i]);
-    pos_mds(x);
 }
+
+GL_HD void pos_permute(gl_t x[12]) { pos_permute_t<false>(x); }

@@ -16,6 +16,12 @@
 #include "poseidon.cuh"
 
 #define POS_BLOCK 128
+#ifndef POS_LEAF_BLOCK
+#define POS_LEAF_BLOCK 128          // threads per CTA of the leaf-hash kernel
+#endif
+#ifndef POS_LEAF_LOCKSTEP
+#define POS_LEAF_LOCKSTEP 0         // 1 = barrier per round so a CTA's warps share instruction fetches (no gain once the code fits: measured -3 %)
+#endif
 
 // load 8 consecutive words of a row (zero beyond `n` words)
 static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restrict__ p, uint32_t n, bool vec16)
@@ -35,16 +41,25 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 }
 
 // out[row*4 .. +4) = linear_hash(in[row*pitch .. +ncols))
-__global__ void __launch_bounds__(POS_BLOCK)
+// LOCKSTEP: every thread of the CTA runs the same number of permutations (rows past the end are clamped to the
+// last row and simply not stored), so the per-round barriers inside pos_permute_t are reached by all.
+template <bool LOCKSTEP>
+__global__ void __launch_bounds__(POS_LEAF_BLOCK)
 k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16)
 {
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= nrows) return;
+    const bool live = row < nrows;
+    if (!live) {
+        if (!LOCKSTEP) return;
+        row = nrows - 1;
+    }
     const gl_t *p = in + row * pitch;
     gl_t *o = out + row * 4;
     if (ncols <= POS_CAP) {                       // size <= CAPACITY: copy and zero-pad, no hashing (:234-239)
+        if (live) {
 #pragma unroll
-        for (int i = 0; i < 4; i++) o[i] = (uint64_t)i < ncols ? gl_canon(p[i]) : 0;
+            for (int i = 0; i < 4; i++) o[i] = (uint64_t)i < ncols ? gl_canon(p[i]) : 0;
+        }
         return;
     }
     gl_t x[12];
@@ -61,12 +76,14 @@ k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t
             uint64_t rem = ncols - 8 * (b + 1);
             pos_load8(nxt, p + 8 * (b + 1), (uint32_t)(rem < 8 ? rem : 8), vec16 != 0);
         }
-        pos_permute(x);
+        pos_permute_t<LOCKSTEP>(x);
 #pragma unroll
         for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
     }
+    if (live) {
 #pragma unroll
-    for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
+        for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
+    }
 }
 
 // parents[i] = H(children[2i] || children[2i+1] || 0000)[0:4]
