@@ -22,6 +22,8 @@
 #define __launch_bounds__(...)
 #define __align__(n) __attribute__((aligned(n)))
 #define GLP_CONSTANT static const
+#define GLP_SET_SMEM(kernel, bytes) ((void)0)
+#define GLP_NOINLINE __attribute__((noinline))
 
 struct dim3 {
     unsigned x, y, z;

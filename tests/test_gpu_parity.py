@@ -174,7 +174,7 @@ def test_ntt_two_pass_large(ctx, oracle, rng):
 def test_ntt_three_pass_and_cb2(ctx, oracle, rng):
     """the 3-pass plan (sizes above 2^24 in production) reached at small sizes by capping the tile; and the
     2-column tile variant"""
-    for env in ({"GLP_NTT_MAX_LOGQ": 5}, {"GLP_NTT_CB": 2}, {"GLP_NTT_CB": 2, "GLP_NTT_MAX_LOGQ": 5}):
+    for env in ({"GLP_NTT_MAX_LOGQ": 5}, {"GLP_NTT_MAX_LOGQ": 4}, {"GLP_NTT_NO_PASS_TABLES": 1}, {"GLP_NTT_NO_FUSED_LDE": 1}, {"GLP_NTT_NO_PASS_TABLES": 1, "GLP_NTT_MAX_LOGQ": 4}):
         c = env_ctx(**env)
         try:
             for n, w in [(1 << 13, 3), (1 << 11, 8), (1 << 6, 1)]:

@@ -39,12 +39,6 @@ struct DevBuf {
     void *p = nullptr;
     size_t bytes = 0;
 };
-struct StepTab {
-    uint32_t nsteps = 0;
-    uint32_t step_log[NTT_MAX_STEPS] = {0, 0, 0, 0};
-    uint32_t ntw = 0;          // words
-    gl_t *tw = nullptr;        // device
-};
 struct TwoLevel {
     gl_t *lo = nullptr, *hi = nullptr;
 };
@@ -55,11 +49,14 @@ struct glp_ctx {
     cudaStream_t copy_stream[2] = {nullptr, nullptr};
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
-    int ntt_cb = 4;
-    uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the 2/3-pass paths at small sizes
-    std::map<uint32_t, StepTab> step_tabs;   // by logQ
+    uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
+    bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
+    bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
     std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
     std::map<uint32_t, TwoLevel> sc_tabs;    // shift^j / N, by logN
+    std::map<uint64_t, gl_t *> pass_tabs;    // per-pass twiddle rows, by (logL, logQ, inverse)
+    std::map<uint64_t, gl_t *> scale_tabs;   // shift^j / N in DIF storage order, by (logN, plan)
+    gl_t *zeta = nullptr;                    // w_256^i
     DevBuf s1, s2;                           // NTT scratch
     DevBuf ext, nodes, tmp_in, tmp_out;      // commit / staging
     DevBuf partial;                          // checksum partials
@@ -143,14 +140,12 @@ extern "C" int glp_init(int device, glp_ctx **out)
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[0], cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[1], cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
-    const char *cb = getenv("GLP_NTT_CB");
-    if (cb && (atoi(cb) == 2 || atoi(cb) == 4)) ctx->ntt_cb = atoi(cb);
     const char *mq = getenv("GLP_NTT_MAX_LOGQ");
     if (mq && atoi(mq) >= 1 && atoi(mq) <= NTT_MAX_LOGQ) ctx->max_logq = (uint32_t)atoi(mq);
-#ifndef GLP_EMU
-    CU(cudaFuncSetAttribute(k_ntt_tile<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    CU(cudaFuncSetAttribute(k_ntt_tile<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-#endif
+    const char *npt = getenv("GLP_NTT_NO_PASS_TABLES");
+    ctx->no_pass_tables = npt && atoi(npt) != 0;
+    const char *nfl = getenv("GLP_NTT_NO_FUSED_LDE");
+    ctx->no_fused_lde = nfl && atoi(nfl) != 0;
     *out = ctx;
     return GLP_OK;
 }
@@ -250,33 +245,6 @@ static int table_alloc(glp_ctx *ctx, size_t words, gl_t **out)
     return GLP_OK;
 }
 
-static int get_step_tab(glp_ctx *ctx, uint32_t logQ, const StepTab **out)
-{
-    auto it = ctx->step_tabs.find(logQ);
-    if (it != ctx->step_tabs.end()) { *out = &it->second; return GLP_OK; }
-    StepTab t;
-    uint32_t rem = logQ % 4, left = logQ;
-    if (rem) { t.step_log[t.nsteps++] = rem; left -= rem; }
-    while (left) { t.step_log[t.nsteps++] = 4; left -= 4; }
-    uint32_t lg = logQ;
-    for (uint32_t s = 0; s + 1 < t.nsteps; s++) { t.ntw += 1u << lg; lg -= t.step_log[s]; }
-    if (t.ntw) {
-        GLP(table_alloc(ctx, t.ntw, &t.tw));
-        gl_t *p = t.tw;
-        lg = logQ;
-        for (uint32_t s = 0; s + 1 < t.nsteps; s++) {
-            const uint32_t n = 1u << lg;
-            LAUNCH_FLAT(ctx, k_ntt_step_table, (n + 127) / 128, 128, p, lg, t.step_log[s]);
-            p += n;
-            lg -= t.step_log[s];
-        }
-        CU(cudaGetLastError());
-    }
-    ctx->step_tabs[logQ] = t;
-    *out = &ctx->step_tabs[logQ];
-    return GLP_OK;
-}
-
 // lo[e] = c * g^e (e < 2^min(logN,12)), hi[h] = g^(h << 12) (h < max(1, N >> 12))
 static int make_two_level(glp_ctx *ctx, uint32_t logN, gl_t c, gl_t g, TwoLevel *t)
 {
@@ -300,16 +268,49 @@ static int get_tw_tab(glp_ctx *ctx, uint32_t logN, const TwoLevel **out)
     *out = &it->second;
     return GLP_OK;
 }
+static gl_t host_ninv(uint32_t logN) { return gl_canon(gl_inv((gl_t)((1ull << logN) % GL_P))); }
 static int get_sc_tab(glp_ctx *ctx, uint32_t logN, const TwoLevel **out)
 {
     auto it = ctx->sc_tabs.find(logN);
     if (it == ctx->sc_tabs.end()) {
         TwoLevel t;
-        const gl_t ninv = gl_canon(gl_inv((gl_t)((1ull << logN) % GL_P)));
-        GLP(make_two_level(ctx, logN, ninv, GL_SHIFT, &t));
+        GLP(make_two_level(ctx, logN, host_ninv(logN), GL_SHIFT, &t));
         it = ctx->sc_tabs.emplace(logN, t).first;
     }
     *out = &it->second;
+    return GLP_OK;
+}
+// w_256^i, i < 256: the step-to-step twiddles of every tile size (w_Q^e = w_256^(e * 256/Q))
+static int get_zeta(glp_ctx *ctx, const gl_t **out)
+{
+    if (!ctx->zeta) {
+        GLP(table_alloc(ctx, 256, &ctx->zeta));
+        LAUNCH_FLAT(ctx, k_ntt_pow_table, 2, 128, ctx->zeta, (gl_t)1, host_root(8), (uint64_t)1, (uint64_t)256);
+        CU(cudaGetLastError());
+    }
+    *out = ctx->zeta;
+    return GLP_OK;
+}
+// Pass table [L/Q][Q] of w_L^(+-p*i): one contiguous row per tile.  NULL (-> two-level tables in the kernel)
+// when the pass needs none (L == Q) or the table would exceed the cap.
+#define NTT_PASS_TABLE_MAX_LOGL 25
+static int get_pass_table(glp_ctx *ctx, uint32_t logL, uint32_t logQ, bool inv, const gl_t **out)
+{
+    *out = nullptr;
+    if (logL <= logQ || logL > NTT_PASS_TABLE_MAX_LOGL || ctx->no_pass_tables) return GLP_OK;
+    const uint64_t key = ((uint64_t)logL << 16) | (logQ << 8) | (inv ? 1 : 0);
+    auto it = ctx->pass_tabs.find(key);
+    if (it == ctx->pass_tabs.end()) {
+        gl_t *t = nullptr;
+        const uint64_t n = 1ull << logL;
+        GLP(table_alloc(ctx, n, &t));
+        gl_t g = host_root(logL);
+        if (inv) g = gl_canon(gl_inv(g));
+        LAUNCH_FLAT(ctx, k_ntt_pass_table, (unsigned)((n + 255) / 256), 256, t, g, logQ, n);
+        CU(cudaGetLastError());
+        it = ctx->pass_tabs.emplace(key, t).first;
+    }
+    *out = it->second;
     return GLP_OK;
 }
 
@@ -322,77 +323,227 @@ extern "C" uint64_t glp_root(uint32_t domain_pow, uint64_t idx)
 // ------------------------------------------------------------------------------------------------
 // NTT passes (K2-K5)
 // ------------------------------------------------------------------------------------------------
-struct PassPlan {
-    uint32_t npass = 0;
-    uint32_t logq[3] = {0, 0, 0};
-};
-static PassPlan plan_passes(const glp_ctx *ctx, uint32_t logN)
+static bool plan_passes(const glp_ctx *ctx, uint32_t logN, NttPlanLogs *pl)
 {
-    PassPlan p;
     const uint32_t mq = ctx->max_logq;
-    if (logN <= mq) { p.npass = 1; p.logq[0] = logN; }
-    else if (logN <= 2 * mq) { p.npass = 2; p.logq[0] = (logN + 1) / 2; p.logq[1] = logN / 2; }
-    else { p.npass = 3; p.logq[0] = (logN + 2) / 3; p.logq[1] = (logN + 1) / 3; p.logq[2] = logN / 3; }
-    return p;
+    memset(pl, 0, sizeof *pl);
+    if (logN == 0) return true;
+    const uint32_t np = (logN + mq - 1) / mq;
+    if (np > NTT_MAX_PASSES) return false;
+    pl->npass = np;
+    for (uint32_t i = 0; i < np; i++) pl->lg[i] = logN / np + (i < logN % np ? 1 : 0);
+    return true;
+}
+// shift^j/N in the storage order the DIF plan `pl` leaves coefficient j in
+static int get_scale_table(glp_ctx *ctx, uint32_t logN, const NttPlanLogs &pl, const gl_t **out)
+{
+    *out = nullptr;
+    if (logN > NTT_PASS_TABLE_MAX_LOGL || ctx->no_pass_tables) return GLP_OK;
+    uint64_t key = logN;
+    for (uint32_t i = 0; i < NTT_MAX_PASSES; i++) key = (key << 8) | (i < pl.npass ? pl.lg[i] : 0);
+    auto it = ctx->scale_tabs.find(key);
+    if (it == ctx->scale_tabs.end()) {
+        gl_t *t = nullptr;
+        const uint64_t n = 1ull << logN;
+        GLP(table_alloc(ctx, n, &t));
+        LAUNCH_FLAT(ctx, k_ntt_scale_table, (unsigned)((n + 255) / 256), 256, t, host_ninv(logN), (gl_t)GL_SHIFT, pl, n);
+        CU(cudaGetLastError());
+        it = ctx->scale_tabs.emplace(key, t).first;
+    }
+    *out = it->second;
+    return GLP_OK;
 }
 
-static size_t ntt_smem_bytes(uint32_t logQ, uint32_t ntw, int cb)
+template <int A, int B>
+static int launch_pass_ab(glp_ctx *ctx, const NttPass &a, bool inv, uint32_t lsh)
 {
-    const size_t Q = (size_t)1 << logQ;
-    return ((Q + (Q >> 4) + 1) * cb + ntw) * sizeof(gl_t);
+    const uint64_t ntiles = 1ull << (a.logN - (A + B));
+    const uint64_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
+    const uint64_t grid = (B == 0 ? (ntiles + NTT_WARPS - 1) / NTT_WARPS : ntiles) * ncg;
+    if (grid > 0x7FFFFFFFull) return fail(GLP_E_ARG, "NTT grid too large");
+    const size_t smem = B == 0 ? 0 : ((size_t)1 << (A + B)) * NTT_LANES * sizeof(gl_t);
+#define NTT_GO(INV, LSH)                                                             \
+    do {                                                                             \
+        auto kfn = k_ntt_pass<A, B, INV, LSH>;                                       \
+        if (smem > 48 * 1024) GLP_SET_SMEM(kfn, smem);                               \
+        LAUNCH(ctx, kfn, (unsigned)grid, NTT_THREADS, smem, a);                      \
+    } while (0)
+    if (inv) NTT_GO(true, 0);
+    else if (A == 4 && lsh == 1) NTT_GO(false, (A == 4 ? 1 : 0));
+    else if (A == 4 && lsh == 2) NTT_GO(false, (A == 4 ? 2 : 0));
+    else if (A == 4 && lsh == 3) NTT_GO(false, (A == 4 ? 3 : 0));
+    else NTT_GO(false, 0);
+#undef NTT_GO
+    return GLP_OK;
+}
+static int launch_pass(glp_ctx *ctx, const NttPass &a, uint32_t lg, bool inv, uint32_t lsh)
+{
+    switch (lg) {
+    case 8: return launch_pass_ab<4, 4>(ctx, a, inv, lsh);
+    case 7: return launch_pass_ab<4, 3>(ctx, a, inv, lsh);
+    case 6: return launch_pass_ab<3, 3>(ctx, a, inv, 0);
+    case 5: return launch_pass_ab<3, 2>(ctx, a, inv, 0);
+    case 4: return launch_pass_ab<4, 0>(ctx, a, inv, lsh);
+    case 3: return launch_pass_ab<3, 0>(ctx, a, inv, 0);
+    case 2: return launch_pass_ab<2, 0>(ctx, a, inv, 0);
+    case 1: return launch_pass_ab<1, 0>(ctx, a, inv, 0);
+    }
+    return fail(GLP_E_ARG, "NTT: bad tile size");
 }
 
-// One transform of size 2^logN on `wb` columns: in (pitch/col0) -> out (pitch/col0), scratch holds 2^logN x wb.
-static int run_transform(glp_ctx *ctx, uint32_t logN, const gl_t *in, uint64_t in_pitch, uint64_t in_col0, gl_t *out,
-                         uint64_t out_pitch, uint64_t out_col0, uint32_t wb, uint64_t live, bool inverse, bool extend,
-                         gl_t *scratch)
+static int copy_canon(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_t *in, uint64_t in_pitch, uint64_t nrows, uint64_t ncols)
 {
-    const PassPlan pl = plan_passes(ctx, logN);
-    const TwoLevel *tw = nullptr, *sc = nullptr;
-    if (pl.npass > 1) GLP(get_tw_tab(ctx, logN, &tw));
-    if (inverse && extend) GLP(get_sc_tab(ctx, logN, &sc));
+    const uint64_t nb = (nrows * ncols + 255) / 256;
+    LAUNCH_FLAT(ctx, k_ntt_copy_canon, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, out, out_pitch, in, in_pitch, nrows, ncols);
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+
+// fields common to every pass of one transform
+static int pass_common(glp_ctx *ctx, NttPass *a, uint32_t logN, uint32_t wb, bool need_two_level)
+{
+    memset(a, 0, sizeof *a);
+    a->ncols = wb;
+    a->logN = logN;
+    GLP(get_zeta(ctx, &a->zeta));
+    if (need_two_level) {
+        const TwoLevel *tw = nullptr;
+        GLP(get_tw_tab(ctx, logN, &tw));
+        a->tw_lo = tw->lo;
+        a->tw_hi = tw->hi;
+    }
+    return GLP_OK;
+}
+
+// Natural order in, natural order out, `wb` columns: in (pitch) -> out (pitch); scratch holds 2^logN x wb words
+// (needed when the plan has more than one pass).  Rows >= live of `in` are zero and never read.
+static int run_transform(glp_ctx *ctx, uint32_t logN, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t wb,
+                         uint64_t live, bool inverse, bool extend, gl_t *scratch)
+{
+    if (logN == 0) return copy_canon(ctx, out, out_pitch, in, in_pitch, 1, wb);     // 1/N = shift^0 = 1
+    NttPlanLogs pl;
+    if (!plan_passes(ctx, logN, &pl)) return fail(GLP_E_ARG, "NTT: size exceeds four tile passes");
     uint32_t logL = logN;
-    for (uint32_t t = 0; t < pl.npass; t++) {
-        const bool first = (t == 0), last = (t + 1 == pl.npass);
-        const StepTab *st = nullptr;
-        GLP(get_step_tab(ctx, pl.logq[t], &st));
+    for (uint32_t i = 0; i < pl.npass; i++) {
+        const bool first = i == 0, last = i + 1 == pl.npass;
         NttPass a;
-        memset(&a, 0, sizeof a);
+        const gl_t *tab = nullptr;
+        if (!last) GLP(get_pass_table(ctx, logL, pl.lg[i], inverse, &tab));
+        GLP(pass_common(ctx, &a, logN, wb, !last && !tab));
         a.in = first ? in : scratch;
         a.in_pitch = first ? in_pitch : wb;
-        a.in_col0 = first ? in_col0 : 0;
         a.out = last ? out : scratch;
         a.out_pitch = last ? out_pitch : wb;
-        a.out_col0 = last ? out_col0 : 0;
-        a.live = first ? live : (1ull << logN);
-        a.wb = wb;
-        a.logN = logN;
-        a.logL = logL;
-        a.logQ = pl.logq[t];
-        a.last = last;
+        a.logL = a.log_in_L = logL;
+        a.live = first ? live : (1ull << logL);
+        a.tw_mode = last ? NTT_TW_NONE : NTT_TW_POST;
+        a.tw = tab;
+        a.scatter = last;
+        a.nprev = i;
+        for (uint32_t k = 0; k < i; k++) a.prev_log[k] = pl.lg[k];
         a.canon_in = first;
-        a.inverse = inverse;
-        a.extend = extend;
-        a.nprev = t;
-        a.logq_prev0 = pl.logq[0];
-        a.logq_prev1 = pl.logq[1];
-        a.nsteps = st->nsteps;
-        for (uint32_t s = 0; s < NTT_MAX_STEPS; s++) a.step_log[s] = st->step_log[s];
-        a.step_tw = st->tw;
-        a.tw_lo = tw ? tw->lo : nullptr;
-        a.tw_hi = tw ? tw->hi : nullptr;
-        a.sc_lo = sc ? sc->lo : nullptr;
-        a.sc_hi = sc ? sc->hi : nullptr;
-        a.ninv = gl_canon(gl_inv((gl_t)((1ull << logN) % GL_P)));
-        const uint64_t S = 1ull << (logL - a.logQ);
-        const int cb = ctx->ntt_cb;
-        const uint64_t nvg = (S * wb + cb - 1) / cb;
-        const uint64_t ntiles = (1ull << (logN - logL)) * nvg;
-        if (ntiles > 0x7FFFFFFFull) return fail(GLP_E_ARG, "NTT grid too large");
-        const size_t smem = ntt_smem_bytes(a.logQ, st->ntw, cb);
-        if (cb == 4) LAUNCH(ctx, k_ntt_tile<4>, (unsigned)ntiles, NTT_THREADS, smem, a);
-        else LAUNCH(ctx, k_ntt_tile<2>, (unsigned)ntiles, NTT_THREADS, smem, a);
-        logL -= a.logQ;
+        a.canon_out = last;
+        if (last && inverse) {
+            if (extend) {
+                const TwoLevel *sc = nullptr;
+                GLP(get_sc_tab(ctx, logN, &sc));
+                a.scale_mode = NTT_SC_TWOLEVEL;
+                a.sc_lo = sc->lo;
+                a.sc_hi = sc->hi;
+            } else {
+                a.scale_mode = NTT_SC_CONST;
+                a.scale_const = host_ninv(logN);
+            }
+        }
+        // compile-time pruning when exactly the upper 1 - 2^-lsh of the first pass's tile rows are zero
+        uint32_t lsh = 0;                                         // rows q*S + p < N >> e  <=>  high digit of q < 16 >> e
+        if (first && !inverse)
+            for (uint32_t e = 1; e <= 3 && e <= logN; e++)
+                if (live == (1ull << (logN - e))) lsh = e;
+        GLP(launch_pass(ctx, a, pl.lg[i], inverse, lsh));
+        logL -= pl.lg[i];
+    }
+    CU(cudaGetLastError());
+    return GLP_OK;
+}
+
+// Low-degree extension of `wb` columns without any reordering pass: INTT decimation-in-frequency (natural in,
+// digit-reversed out, in place in scratch S = 2^logN x wb), coset scaling on its last pass, then the size-2^(logN+e)
+// forward NTT decimation-in-time with the same radices, reading S and finishing in place in `out`.
+// Returns 1 when the shape has no such plan (caller falls back to two natural-order transforms).
+static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t wb,
+                   gl_t *S)
+{
+    const uint32_t logM = logN + e;
+    NttPlanLogs q, r;
+    if (!plan_passes(ctx, logM, &q) || q.npass == 0) return 1;
+    if (q.lg[q.npass - 1] < e) return 1;
+    r = q;
+    r.lg[r.npass - 1] -= e;
+    if (r.lg[r.npass - 1] == 0) r.npass--;
+    // ---- INTT, DIF, in place in S ----
+    {
+        ProfScope ps(ctx, 0);
+        if (r.npass == 0) GLP(copy_canon(ctx, S, wb, in, in_pitch, 1, wb));
+        const gl_t *sct = nullptr;
+        if (r.npass) GLP(get_scale_table(ctx, logN, r, &sct));
+        uint32_t logL = logN;
+        for (uint32_t i = 0; i < r.npass; i++) {
+            const bool first = i == 0, last = i + 1 == r.npass;
+            NttPass a;
+            const gl_t *tab = nullptr;
+            if (!last) GLP(get_pass_table(ctx, logL, r.lg[i], true, &tab));
+            GLP(pass_common(ctx, &a, logN, wb, !last && !tab));
+            a.in = first ? in : S;
+            a.in_pitch = first ? in_pitch : wb;
+            a.out = S;
+            a.out_pitch = wb;
+            a.logL = a.log_in_L = logL;
+            a.live = 1ull << logL;
+            a.tw_mode = last ? NTT_TW_NONE : NTT_TW_POST;
+            a.tw = tab;
+            a.nprev = i;
+            for (uint32_t k = 0; k < i; k++) a.prev_log[k] = r.lg[k];
+            a.canon_in = first;
+            if (last) {
+                if (sct) { a.scale_mode = NTT_SC_TABLE; a.sc = sct; }
+                else {
+                    const TwoLevel *sc = nullptr;
+                    GLP(get_sc_tab(ctx, logN, &sc));
+                    a.scale_mode = NTT_SC_TWOLEVEL;
+                    a.sc_lo = sc->lo;
+                    a.sc_hi = sc->hi;
+                }
+            }
+            GLP(launch_pass(ctx, a, r.lg[i], true, 0));
+            logL -= r.lg[i];
+        }
+    }
+    // ---- forward NTT of size 2^logM, DIT: last digit (contiguous rows) first ----
+    {
+        ProfScope ps(ctx, 1);
+        uint32_t logL = 0;
+        for (int i = (int)q.npass - 1; i >= 0; i--) {
+            logL += q.lg[i];
+            const bool first = i == (int)q.npass - 1, last = i == 0;
+            NttPass a;
+            const gl_t *tab = nullptr;
+            if (!first) GLP(get_pass_table(ctx, logL, q.lg[i], false, &tab));
+            GLP(pass_common(ctx, &a, logM, wb, !first && !tab));
+            a.in = first ? S : out;
+            a.in_pitch = first ? wb : out_pitch;
+            a.out = out;
+            a.out_pitch = out_pitch;
+            a.logL = logL;
+            a.log_in_L = first ? logL - e : logL;
+            a.live = first ? (1ull << (logL - e)) : (1ull << logL);
+            a.tw_mode = first ? NTT_TW_NONE : NTT_TW_PRE;
+            a.tw = tab;
+            a.canon_out = last;
+            uint32_t lsh = 0;
+            if (first && e >= 1 && e <= 3) lsh = e;              // used by the kernels whose high digit of q is 4 bits wide
+            GLP(launch_pass(ctx, a, q.lg[i], false, lsh));
+        }
     }
     CU(cudaGetLastError());
     return GLP_OK;
@@ -412,8 +563,7 @@ static uint32_t pick_block_cols(glp_ctx *ctx, uint64_t rows_total, uint64_t ncol
 {
     uint64_t wb = scratch_budget(ctx) / (rows_total * sizeof(gl_t));
     if (wb >= ncols) return (uint32_t)ncols;
-    if (wb >= 64) wb = 64 * (wb / 64);
-    else if (wb >= 8) wb = 8 * (wb / 8);
+    if (wb >= 32) wb = 32 * (wb / 32);
     if (wb < 1) wb = 1;
     return (uint32_t)wb;
 }
@@ -423,7 +573,8 @@ static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src,
                    bool inverse, bool extend)
 {
     const uint32_t logN = ilog2_u64(size);
-    const PassPlan pl = plan_passes(ctx, logN);
+    NttPlanLogs pl;
+    if (!plan_passes(ctx, logN, &pl)) return fail(GLP_E_ARG, "NTT: size exceeds four tile passes");
     uint32_t wb = (uint32_t)ncols;
     if (pl.npass > 1) {
         wb = pick_block_cols(ctx, size, ncols);
@@ -431,7 +582,29 @@ static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src,
     }
     for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
         const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-        GLP(run_transform(ctx, logN, src, src_pitch, c0, dst, dst_pitch, c0, w, size, inverse, extend, (gl_t *)ctx->s1.p));
+        GLP(run_transform(ctx, logN, src + c0, src_pitch, dst + c0, dst_pitch, w, size, inverse, extend, (gl_t *)ctx->s1.p));
+    }
+    return GLP_OK;
+}
+
+// one column block of the extension: in (n rows) -> out (n_ext rows); S holds n x w words, S2 n_ext x w (fallback only)
+static int lde_block(glp_ctx *ctx, uint32_t logN, uint32_t logE, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t w)
+{
+    const uint64_t n = 1ull << logN, n_ext = 1ull << logE;
+    GLP(ensure(ctx, ctx->s2, (size_t)n * w * sizeof(gl_t)));
+    int rc = ctx->no_fused_lde ? 1 : run_lde(ctx, logN, logE - logN, in, in_pitch, out, out_pitch, w, (gl_t *)ctx->s2.p);
+    if (rc != 1) return rc;
+    // fallback: two natural-order transforms (INTT with coset scaling, then the zero-padded forward NTT)
+    NttPlanLogs pe;
+    if (!plan_passes(ctx, logE, &pe)) return fail(GLP_E_ARG, "NTT: size exceeds four tile passes");
+    GLP(ensure(ctx, ctx->s1, (size_t)n_ext * w * sizeof(gl_t)));
+    {
+        ProfScope ps(ctx, 0);
+        GLP(run_transform(ctx, logN, in, in_pitch, (gl_t *)ctx->s2.p, w, w, n, true, true, (gl_t *)ctx->s1.p));
+    }
+    {
+        ProfScope ps(ctx, 1);
+        GLP(run_transform(ctx, logE, (gl_t *)ctx->s2.p, w, out, out_pitch, w, n, false, false, (gl_t *)ctx->s1.p));
     }
     return GLP_OK;
 }
@@ -440,22 +613,10 @@ static int dev_extend_pol(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_
                           uint64_t ncols)
 {
     const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
-    const uint32_t wb = pick_block_cols(ctx, n_ext + n, ncols);
-    GLP(ensure(ctx, ctx->s1, (size_t)n_ext * wb * sizeof(gl_t)));
-    GLP(ensure(ctx, ctx->s2, (size_t)n * wb * sizeof(gl_t)));
-    gl_t *s1 = (gl_t *)ctx->s1.p, *s2 = (gl_t *)ctx->s2.p;
+    const uint32_t wb = pick_block_cols(ctx, ctx->no_fused_lde ? n_ext + n : n, ncols);
     for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
         const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-        // coefficients * shift^j / N  (INTT with extend, ntt_goldilocks.cpp:345)
-        {
-            ProfScope ps(ctx, 0);
-            GLP(run_transform(ctx, logN, in, in_pitch, c0, s2, w, 0, w, n, true, true, s1));
-        }
-        // zero-padded forward transform of size n_ext (ntt_goldilocks.cpp:346)
-        {
-            ProfScope ps(ctx, 1);
-            GLP(run_transform(ctx, logE, s2, w, 0, out, out_pitch, c0, w, n, false, false, s1));
-        }
+        GLP(lde_block(ctx, logN, logE, in + c0, in_pitch, out + c0, out_pitch, w));
     }
     return GLP_OK;
 }
@@ -483,7 +644,7 @@ extern "C" int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_
     if (!src) return fail(GLP_E_ARG, "glp_ntt: src is NULL");
     if (!is_pow2(size)) return fail(GLP_E_ARG, "glp_ntt: size is not a power of two");
     if (size > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
-    if (ilog2_u64(size) > 3 * ctx->max_logq) return fail(GLP_E_ARG, "glp_ntt: size exceeds three tile passes");
+    if (ilog2_u64(size) > NTT_MAX_PASSES * ctx->max_logq) return fail(GLP_E_ARG, "glp_ntt: size exceeds four tile passes");
     if (!dst) dst = (uint64_t *)src;                            // ntt_goldilocks.cpp:15-22
     CU(cudaSetDevice(ctx->device));
     const size_t words = (size_t)size * ncols;
@@ -766,18 +927,9 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
             const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
             if (k + 1 < nblocks) GLP(upload(k + 1));
             CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
-            GLP(ensure(ctx, ctx->s1, (size_t)n_ext * wb * sizeof(gl_t)));
-            GLP(ensure(ctx, ctx->s2, (size_t)n * wb * sizeof(gl_t)));
-            const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
-            {
-                ProfScope ps(ctx, 0);
-                GLP(run_transform(ctx, logN, stage[k & 1], w, 0, (gl_t *)ctx->s2.p, w, 0, w, n, true, true, (gl_t *)ctx->s1.p));
-            }
+            // (the staging buffer is free again once the block's INTT has read it; for simplicity it is released after the block)
+            GLP(lde_block(ctx, ilog2_u64(n), ilog2_u64(n_ext), stage[k & 1], w, dext + c0, ncols, w));
             CU(cudaEventRecord(free_stage[k], ctx->stream));
-            {
-                ProfScope ps(ctx, 1);
-                GLP(run_transform(ctx, logE, (gl_t *)ctx->s2.p, w, 0, dext, ncols, c0, w, n, false, false, (gl_t *)ctx->s1.p));
-            }
             CU(cudaEventRecord(done[k], ctx->stream));
             if (out_ext && !ext_dev) {
                 CU(cudaStreamWaitEvent(ctx->copy_stream[1], done[k], 0));

@@ -15,4 +15,6 @@
 #define GLP_LAUNCH_FLAT(kernel, grid, block, stream, ...) kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__)
 #define GLP_DYN_SMEM(type, name) extern __shared__ __align__(16) unsigned char name##_raw[]; type *name = reinterpret_cast<type *>(name##_raw)
 #define GLP_CONSTANT __constant__
+#define GLP_NOINLINE __noinline__
+#define GLP_SET_SMEM(kernel, bytes) CU(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)))
 #endif

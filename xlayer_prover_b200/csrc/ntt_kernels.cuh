@@ -1,70 +1,85 @@
 // K1-K5 -- Goldilocks NTT / INTT / low-degree extension over row-major [rows x cols] matrices.
 //
 // Replaces NTT_Goldilocks::{NTT, INTT, extendPol, reversePermutation, computeR} and the twiddle tables of its
-// constructor (src/goldilocks/src/ntt_goldilocks.hpp:49-136,153-165; ntt_goldilocks.cpp:12-352).  Same maths,
-// different algorithm:
+// constructor (src/goldilocks/src/ntt_goldilocks.hpp:49-136,153-165; ntt_goldilocks.cpp:12-352).  Same maths
 //
-//   out[k,:] = sum_i in[i,:] * w^(i k)          (natural order in and out, w = W[log2 N])
-//   inverse  : the same forward transform, written to row (N-k) mod N and scaled by 1/N
-//              (* shift^row when `extend`), exactly the reference's last inverse phase
-//              (ntt_goldilocks.cpp:122-150) -- so no inverse twiddles exist anywhere.
+//   forward : out[k,:] = sum_i in[i,:] * w^(i k)            (w = W[log2 N], natural order in and out)
+//   inverse : out[j,:] = 1/N * sum_k in[k,:] * w^(-j k)     (* shift^j when `extend`, ntt_goldilocks.cpp:122-150)
 //
-// B200 design (see DESIGN.md "LDE"):
-//  * The reference layout (element (i,c) at a[i*ncols+c]) is already batch-contiguous: adjacent columns are
-//    adjacent words.  A tile = Q rows (Q <= 4096) x CB adjacent (virtual) columns, so every global access is a
-//    full 32-byte sector per row and NO transposes or bit-reversal passes over HBM exist at all.  A row
-//    permutation costs nothing at sector granularity, so bit reversal is folded into where a tile stores.
-//  * Decimation in frequency, mixed radix.  log2 N is split into at most three tile passes of <= 12 bits
-//    (2^24 = 2^12 * 2^12: two passes; HBM traffic 2 reads + 2 writes per element).  Pass t gathers rows
-//    b*L + p + m*(L/Q) (m < Q), runs a Q-point transform in shared memory, multiplies output u by w_L^(p u)
-//    and writes it back to row b*L + u*(L/Q) + p -- in place on the row set it read.  The last pass (L == Q)
-//    scatters to the natural row index.  "Virtual columns" v = p*wb + col make strided passes look like a
-//    plain [Q x (L/Q)*wb] matrix, so narrow inputs (1 column) still move whole sectors.
-//  * Inside a tile the Q-point transform is radix-16 steps held in registers (16 values per thread, one
-//    shared-memory round trip per 4 butterfly stages).  Because W[6] = 8, every twiddle INSIDE a 16-point
-//    butterfly is a power of two: gl_mul_pow2 (shifts + one fold), no multiplier, no table.
-//    Only the step-to-step twiddles w_Ls^(p u) are real multiplies; they come from per-step tables laid out
-//    [u][p] so that a warp reads consecutive words.  Shared rows are padded by one row per 16 so the last
-//    step's stride-16 row accesses stay conflict-free.
-//  * Zero padding of the LDE (reversePermutation's zero-fill, ntt_goldilocks.cpp:259-277) is the `live`
-//    row bound of the first pass: rows >= live are never read.
-//  * Pass-to-pass twiddles w_N^e and the coset scaling shift^j / N come from two-level tables
-//    (hi[e >> 12] * lo[e & 4095], 2 x 32 KB for N = 2^24) instead of the reference's N-entry arrays
-//    (134 MB at 2^24, rebuilt on every extendPol call, ntt_goldilocks.cpp:328).
+// but a different algorithm, chosen for the B200 (DESIGN.md "LDE"):
+//
+//  * LANE = COLUMN.  The reference layout (element (i,c) at a[i*ncols+c]) makes adjacent columns adjacent
+//    words, and every column is an independent transform.  A warp owns 32 adjacent columns: each row access
+//    of a warp is one contiguous 256-byte segment (two full lines), every twiddle factor is the same for all
+//    32 lanes (it depends on the row only) and is fetched once per warp, shared-memory accesses are
+//    conflict-free by construction, and no transpose or bit-reversal pass over HBM exists at all.
+//  * A tile = Q <= 256 rows x 32 columns (64 KB of shared memory), transformed by two in-register radix-2^A /
+//    radix-2^B steps (A,B <= 4) with ONE shared-memory exchange between them.  A transform of 2^n rows is
+//    ceil(n/8) tile passes; pass t works on rows  b*L + q*(L/Q) + p  (q < Q) and is in place on that row set.
+//  * Because W[6] = 8, every twiddle INSIDE a 16-point butterfly is a power of two: shifts and one fold
+//    (gl_mul_pow2 with a compile-time exponent), no multiplier.  Real multiplies remain only between the two
+//    steps of a tile (w_Q^(b u), from a 256-entry table) and between passes (w_L^(p k), one contiguous 2 KB
+//    table row per tile).  The inverse transform is the same code with the output registers relabelled
+//    (u -> -u mod 2^A) and the inverse tables.
+//  * Low-degree extension without any reordering pass: the INTT runs decimation-in-frequency (natural in,
+//    digit-reversed out, twiddle after the butterflies), the size-N_ext forward NTT runs decimation-in-time
+//    (digit-reversed in, natural out, twiddle before the butterflies) with the same radices, so the INTT's
+//    output IS the NTT's input order.  The coset scaling shift^j/N is applied to the INTT's last pass from a
+//    table laid out in that storage order.  The zero padding (reversePermutation's zero-fill,
+//    ntt_goldilocks.cpp:259-277) is never materialised: with blowup 2^e each contiguous run of Q3 input rows
+//    of the NTT's first pass has its last Q3 - Q3/2^e rows identically zero; they are not read and the
+//    butterflies that would touch them are pruned at compile time (LSH template parameter).
 #pragma once
 #include "cuda_compat.h"
 #include "gl_field.cuh"
 
-#define NTT_MAX_LOGQ 12
+#define NTT_MAX_LOGQ 8              // tile rows <= 2^8
 #define NTT_LOGT 12                 // two-level tables: low 12 bits / the rest
-#define NTT_THREADS 256
-#define NTT_MAX_STEPS 4
+#define NTT_WARPS 16
+#define NTT_LANES 32
+#define NTT_THREADS (NTT_WARPS * NTT_LANES)
+#define NTT_MAX_PASSES 4
+
+enum { NTT_TW_NONE = 0, NTT_TW_PRE = 1, NTT_TW_POST = 2 };
+enum { NTT_SC_NONE = 0, NTT_SC_CONST = 1, NTT_SC_TABLE = 2, NTT_SC_TWOLEVEL = 3 };
 
 struct NttPass {
-    const gl_t *in;
+    const gl_t *in;                  // first column of this column block
     gl_t *out;
     uint64_t in_pitch, out_pitch;    // words per row
-    uint64_t in_col0, out_col0;      // first column of this block inside a row of in / out
-    uint64_t live;                   // rows >= live of `in` are zero (first pass of an extension)
-    uint32_t wb;                     // columns in this block
-    uint32_t logN, logL, logQ;       // whole transform, sub-transform this pass splits, tile size
-    uint32_t last;                   // last pass: scatter to natural order (+ inverse handling)
-    uint32_t canon_in;               // first pass: inputs may be non-canonical
-    uint32_t inverse, extend;
-    uint32_t nprev, logq_prev0, logq_prev1;   // tile sizes of the earlier passes (for the output index)
-    uint32_t nsteps, step_log[NTT_MAX_STEPS]; // radix (log2) of each in-tile step
-    const gl_t *step_tw;             // per-step twiddles, concatenated, step s laid out [u][p]
-    const gl_t *tw_lo, *tw_hi;       // w_N^e  = tw_hi[e >> 12] * tw_lo[e & 4095]
-    const gl_t *sc_lo, *sc_hi;       // shift^j / N = sc_hi[j >> 12] * sc_lo[j & 4095]   (extend)
-    gl_t ninv;                       // 1/N (inverse without extend)
+    uint32_t ncols;                  // columns in this block (lanes past the end idle)
+    uint32_t logN, logL;             // whole transform; sub-transform this pass splits (tile stride = L/Q)
+    uint32_t log_in_L;               // input rows per sub-transform: logL, or logL - e for the zero-padded first DIT pass
+    uint64_t live;                   // input rows >= live of each sub-transform are zero and never read
+    uint32_t tw_mode;                // NTT_TW_*
+    const gl_t *tw;                  // [L/Q][Q]: w_L^(+-p*i); NULL -> two-level tables below
+    const gl_t *tw_lo, *tw_hi;       // w_N^e = tw_hi[e >> 12] * tw_lo[e & 4095]   (forward root; the inverse negates e)
+    const gl_t *zeta;                // w_256^i, i < 256  (step-to-step twiddles of a tile)
+    uint32_t scale_mode;             // NTT_SC_*
+    gl_t scale_const;                // 1/N
+    const gl_t *sc;                  // NTT_SC_TABLE: shift^j/N indexed by the storage position of coefficient j
+    const gl_t *sc_lo, *sc_hi;       // NTT_SC_TWOLEVEL: shift^j/N = sc_hi[j >> 12] * sc_lo[j & 4095], j natural
+    uint32_t scatter;                // last DIF pass: store to the natural row index instead of in place
+    uint32_t nprev, prev_log[NTT_MAX_PASSES - 1];   // tile sizes (log2) of the earlier passes, for the natural index
+    uint32_t canon_in, canon_out;
 };
 
+static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
+static constexpr __host__ __device__ int ntt_cbitrev(int x, int bits)
+{
+    int r = 0;
+    for (int i = 0; i < bits; i++) r |= ((x >> i) & 1) << (bits - 1 - i);
+    return r;
+}
+
 // ---- in-register 2^LOG-point DIF transform, twiddles are powers of two ----
-// v[i] <- sum_m v[m] * w^(m * bitrev(i)),  w = W[LOG] = 2^(192 / 2^LOG)   (W[4]=2^12, W[3]=2^24, W[2]=2^48, W[1]=2^96=-1)
-template <int LOG>
+// v[bitrev(u)] <- sum_m v[m] * w^(m u),  w = W[LOG] = 2^(192 / 2^LOG)   (W[4]=2^12, W[3]=2^24, W[2]=2^48, W[1]=2^96=-1)
+// LSH: inputs with index >= (2^LOG >> LSH) are zero (not even initialised); butterflies on them are pruned.
+template <int LOG, int LSH>
 static __device__ __forceinline__ void ntt_dft_regs(gl_t *v)
 {
     constexpr int Q = 1 << LOG;
+    constexpr int LIVE = Q >> LSH;
 #pragma unroll
     for (int t = 0; t < LOG; t++) {
         const int h = Q >> (t + 1);                 // half size of this stage's butterflies
@@ -73,148 +88,202 @@ static __device__ __forceinline__ void ntt_dft_regs(gl_t *v)
         for (int g = 0; g < Q; g += 2 * h) {
 #pragma unroll
             for (int j = 0; j < h; j++) {
-                gl_t a = v[g + j], b = v[g + j + h];
-                v[g + j] = gl_add(a, b);
-                gl_t d = gl_sub(a, b);
-                v[g + j + h] = (j == 0) ? d : gl_mul_pow2(d, (unsigned)(tshift * j));
+                if (LIVE <= h) {                    // upper input is zero: (a + 0, (a - 0) w^j)
+                    if (j < LIVE) {
+                        const gl_t a = v[g + j];
+                        v[g + j + h] = (j == 0) ? a : gl_mul_pow2(a, (unsigned)(tshift * j));
+                    } else {
+                        v[g + j] = 0;
+                        v[g + j + h] = 0;
+                    }
+                } else {
+                    const gl_t a = v[g + j], b = v[g + j + h];
+                    v[g + j] = gl_add(a, b);
+                    const gl_t d = gl_sub(a, b);
+                    v[g + j + h] = (j == 0) ? d : gl_mul_pow2(d, (unsigned)(tshift * j));
+                }
             }
         }
     }
 }
-
-static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
-
-// physical shared-memory row of logical row r: one pad row per 16
-static __device__ __forceinline__ uint32_t ntt_phys(uint32_t r) { return r + (r >> 4); }
-
-template <int LOG, int CB>
-static __device__ __forceinline__ void ntt_tile_step(gl_t *data, const gl_t *tw, uint32_t logQ, uint32_t logLs, bool last_step)
+// register that holds output u of ntt_dft_regs; the inverse transform's output u is the forward one's -u
+template <int LOG, bool INV>
+static constexpr __host__ __device__ int ntt_slot(int u)
 {
-    constexpr int QS = 1 << LOG;
-    const uint32_t logStride = logLs - LOG;          // Ls / Qs
-    const uint32_t stride = 1u << logStride;
-    const uint32_t ngroups = ((1u << logQ) >> LOG) * CB;
-    for (uint32_t g = threadIdx.x; g < ngroups; g += blockDim.x) {
-        const uint32_t c = g % CB, rest = g / CB;
-        const uint32_t pp = rest & (stride - 1), bb = rest >> logStride;
-        const uint32_t base = (bb << logLs) + pp;
-        gl_t v[QS];
-#pragma unroll
-        for (int m = 0; m < QS; m++) v[m] = data[ntt_phys(base + ((uint32_t)m << logStride)) * CB + c];
-        ntt_dft_regs<LOG>(v);
-#pragma unroll
-        for (int i = 0; i < QS; i++) {
-            const uint32_t u = ntt_bitrev((uint32_t)i, LOG);   // v[i] holds output u
-            gl_t x = v[i];
-            if (!last_step && u != 0) x = gl_mul(x, tw[(u << logStride) + pp]);
-            data[ntt_phys(base + (u << logStride)) * CB + c] = x;
-        }
-    }
+    return ntt_cbitrev(INV ? (((1 << LOG) - u) & ((1 << LOG) - 1)) : u, LOG);
 }
 
 // w_N^e from the two-level table
 static __device__ __forceinline__ gl_t ntt_tw2(const gl_t *lo, const gl_t *hi, uint64_t e)
 {
-    gl_t l = __ldg(lo + (e & ((1u << NTT_LOGT) - 1)));
-    uint64_t h = e >> NTT_LOGT;
+    const gl_t l = __ldg(lo + (e & ((1u << NTT_LOGT) - 1)));
+    const uint64_t h = e >> NTT_LOGT;
     return h ? gl_mul(l, __ldg(hi + h)) : l;
 }
 
-// One tile pass.  grid.x = (N / Q) * ceil((L/Q) * wb / CB)
-template <int CB>
-__global__ void __launch_bounds__(NTT_THREADS)
-k_ntt_tile(NttPass a)
+// ---- slow paths, kept out of line so that the unrolled fast path stays small (the kernel must fit the
+// instruction cache: a first version with these inlined at all 48 load/store sites was 190 KB of SASS and
+// spent 5 of every 11 issue cycles waiting for instruction fetch) ----
+// factor kinds of the slow path
+enum { NTT_F_TW = 0, NTT_F_TW_INV = 1, NTT_F_SCALE2 = 2, NTT_F_CONST = 3 };
+struct NttSlow {                       // what the slow path needs, by value (a pointer to the kernel parameter would force a stack copy)
+    const gl_t *tw_lo, *tw_hi, *sc_lo, *sc_hi;
+    gl_t scale_const;
+    uint32_t logN, logL;
+};
+static __device__ GLP_NOINLINE gl_t ntt_factor_slow(NttSlow a, uint32_t kind, uint64_t p, uint64_t idx)
 {
-    GLP_DYN_SMEM(gl_t, smem);
-    const uint32_t Q = 1u << a.logQ;
-    const uint32_t logS = a.logL - a.logQ;                       // stride L/Q between a tile's rows
-    const uint64_t S = 1ull << logS;
-    const uint64_t nvirt = S * a.wb;                             // virtual columns per sub-block
-    const uint64_t nvg = (nvirt + CB - 1) / CB;
-    const uint64_t tile = blockIdx.x;
-    const uint64_t b = tile / nvg, vg = tile % nvg;
-    gl_t *data = smem;                                           // [(Q + Q/16) rows][CB]
-    gl_t *stw = smem + (size_t)(Q + (Q >> 4) + 1) * CB;          // step twiddles
+    if (kind == NTT_F_CONST) return a.scale_const;
+    if (kind == NTT_F_SCALE2) return ntt_tw2(a.sc_lo, a.sc_hi, idx);              // idx = natural coefficient index
+    const uint64_t nmask = (1ull << a.logN) - 1;
+    uint64_t e = ((p * idx) << (a.logN - a.logL)) & nmask;                         // w_L^(p i) = w_N^(p i N/L)
+    if (kind == NTT_F_TW_INV) e = (0 - e) & nmask;
+    return ntt_tw2(a.tw_lo, a.tw_hi, e);
+}
 
-    // step twiddles -> shared
-    uint32_t ntw = 0;
-    {
-        uint32_t lg = a.logQ;
-        for (uint32_t s = 0; s + 1 < a.nsteps; s++) { ntw += 1u << lg; lg -= a.step_log[s]; }
-    }
-    for (uint32_t i = threadIdx.x; i < ntw; i += blockDim.x) stw[i] = __ldg(a.step_tw + i);
-
-    // this thread's column is fixed: blockDim.x is a multiple of CB
-    const uint32_t c = threadIdx.x % CB;
-    const uint64_t v = vg * CB + c;
-    const bool colok = v < nvirt;
-    const uint64_t p = colok ? v / a.wb : 0;
-    const uint32_t col = colok ? (uint32_t)(v % a.wb) : 0;
-    const uint64_t row0 = (b << a.logL) + p;
-
-    // gather rows row0 + m*S
-    for (uint32_t m = threadIdx.x / CB; m < Q; m += blockDim.x / CB) {
-        gl_t x = 0;
-        const uint64_t row = row0 + ((uint64_t)m << logS);
-        if (colok && row < a.live) {
-            x = a.in[row * a.in_pitch + a.in_col0 + col];   // plain load: middle passes run in place
-            if (a.canon_in) x = gl_canon(x);
+// Outputs of a tile pass -> memory.  Output w (w < 2^LOGX) of the last in-register transform sits in
+// v[ntt_slot<LOGX, INV>(w)] and is tile output t = t0 + w * tstride.  Each output is multiplied by at most one
+// factor (the pass twiddle w_L^(+-p t) of a DIF pass, or the scaling of a last inverse pass), read from a table
+// row (fptr[t << fsh]) or produced by the slow path, and stored at row rbase + (t << rsh).
+template <int LOGX, bool INV>
+static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const NttSlow &sl, gl_t *v, uint32_t t0, uint32_t tstride, uint64_t p, bool mul,
+                                                         const gl_t *fptr, uint32_t fsh, uint32_t fkind, uint64_t fbase, uint32_t fbsh,
+                                                         uint64_t rbase, uint32_t rsh, uint32_t col, bool colok)
+{
+    constexpr int QX = 1 << LOGX;
+    if (mul) {
+#pragma unroll
+        for (int w = 0; w < QX; w++) {
+            const uint32_t t = t0 + (uint32_t)w * tstride;
+            const gl_t f = fptr ? __ldg(fptr + ((uint64_t)t << fsh)) : ntt_factor_slow(sl, fkind, p, fbase + ((uint64_t)t << fbsh));
+            gl_t &x = v[ntt_slot<LOGX, INV>(w)];
+            x = gl_mul(x, f);
         }
-        data[ntt_phys(m) * CB + c] = x;
     }
+    if (a.canon_out) {
+#pragma unroll
+        for (int w = 0; w < QX; w++) v[w] = gl_canon(v[w]);
+    }
+    if (!colok) return;
+    gl_t *o = a.out + (rbase + ((uint64_t)t0 << rsh)) * a.out_pitch + col;
+    const uint64_t step = ((uint64_t)tstride << rsh) * a.out_pitch;
+#pragma unroll
+    for (int w = 0; w < QX; w++) o[(uint64_t)w * step] = v[ntt_slot<LOGX, INV>(w)];
+}
+
+// One tile pass.  A, B: log2 radix of the two in-register steps (B == 0: single step, no shared memory).
+// grid.x = tiles * ceil(ncols / 32) (column group fastest, so neighbouring CTAs touch neighbouring segments of
+// the same rows); B == 0 packs NTT_WARPS tiles into a CTA.
+template <int A, int B, bool INV, int LSH>
+__global__ void __launch_bounds__(NTT_THREADS, 2)
+k_ntt_pass(NttPass a)
+{
+    constexpr int QA = 1 << A, QB = 1 << B, LOGQ = A + B;
+    GLP_DYN_SMEM(gl_t, tile);                                    // [Q][32] when B > 0
+    const uint32_t lane = threadIdx.x % NTT_LANES, warp = threadIdx.x / NTT_LANES;
+    const uint32_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
+    const uint64_t ntiles = 1ull << (a.logN - LOGQ);
+    const uint32_t cg = blockIdx.x % ncg;
+    uint64_t tix = blockIdx.x / ncg;
+    if (B == 0) {
+        tix = tix * NTT_WARPS + warp;
+        if (tix >= ntiles) return;                               // no barrier in the single-step kernel
+    }
+    const uint32_t logS = a.logL - LOGQ;
+    const uint64_t p = tix & ((1ull << logS) - 1), bb = tix >> logS;
+    const uint32_t col = cg * NTT_LANES + lane;
+    const bool colok = col < a.ncols;
+    const gl_t *twp = a.tw ? a.tw + (p << LOGQ) : nullptr;
+    const uint64_t posbase = (bb << a.logL) + p;
+    // natural index of tile output t: kbase + (t << ksh); digit k_i of pass i has weight Q_0...Q_(i-1)
+    uint64_t kbase = 0;
+    uint32_t ksh = 0;
+    if (a.scatter || a.scale_mode == NTT_SC_TWOLEVEL) {
+        for (uint32_t i = 0; i < a.nprev; i++) ksh += a.prev_log[i];
+        uint64_t rem = bb;
+        uint32_t sh = ksh;
+        for (int i = (int)a.nprev - 1; i >= 0; i--) {
+            sh -= a.prev_log[i];
+            kbase |= (rem & ((1ull << a.prev_log[i]) - 1)) << sh;
+            rem >>= a.prev_log[i];
+        }
+    }
+    // the one factor each output may be multiplied by, and where outputs go
+    bool omul = false;
+    const gl_t *fptr = nullptr;
+    uint32_t fsh = 0, fkind = 0, fbsh = 0;
+    uint64_t fbase = 0;
+    if (a.tw_mode == NTT_TW_POST && p != 0) { omul = true; fptr = twp; fkind = INV ? NTT_F_TW_INV : NTT_F_TW; }
+    else if (a.scale_mode == NTT_SC_CONST) { omul = true; fkind = NTT_F_CONST; }
+    else if (a.scale_mode == NTT_SC_TABLE) { omul = true; fptr = a.sc + posbase; fsh = logS; }
+    else if (a.scale_mode == NTT_SC_TWOLEVEL) { omul = true; fkind = NTT_F_SCALE2; fbase = kbase; fbsh = ksh; }
+    const uint64_t rbase = a.scatter ? kbase : posbase;
+    const uint32_t rsh = a.scatter ? ksh : logS;
+    const uint64_t in_step = ((uint64_t)QB << logS) * a.in_pitch;   // between consecutive high digits m of q = m*QB + b
+    const bool pre = a.tw_mode == NTT_TW_PRE && p != 0;
+    const NttSlow sl = {a.tw_lo, a.tw_hi, a.sc_lo, a.sc_hi, a.scale_const, a.logN, a.logL};
+
+    // ---- step 1: 2^A-point transforms over the high digit of q = m*QB + b ----
+#pragma unroll 1
+    for (uint32_t b = (B == 0 ? 0 : warp); b < (uint32_t)QB; b += NTT_WARPS) {
+        gl_t v[QA];
+        {
+            const uint64_t r0 = ((uint64_t)b << logS) + p;       // input row of m = 0 inside the sub-transform
+            const gl_t *in = a.in + ((bb << a.log_in_L) + r0) * a.in_pitch + col;
+            const uint64_t rstep = (uint64_t)QB << logS;
+#pragma unroll
+            for (int m = 0; m < (QA >> LSH); m++)
+                v[m] = (colok && r0 + (uint64_t)m * rstep < a.live) ? in[(uint64_t)m * in_step] : 0;   // plain load: middle passes run in place
+        }
+        if (a.canon_in) {
+#pragma unroll
+            for (int m = 0; m < (QA >> LSH); m++) v[m] = gl_canon(v[m]);
+        }
+        if (pre) {                                               // w_L^(+-p q)
+#pragma unroll
+            for (int m = 0; m < (QA >> LSH); m++) {
+                const uint32_t q = (uint32_t)m * QB + b;
+                const gl_t f = twp ? __ldg(twp + q) : ntt_factor_slow(sl, INV ? NTT_F_TW_INV : NTT_F_TW, p, q);
+                v[m] = gl_mul(v[m], f);
+            }
+        }
+        ntt_dft_regs<A, LSH>(v);
+        if (B == 0) {
+            ntt_store_outputs<A, INV>(a, sl, v, 0, 1, p, omul, fptr, fsh, fkind, fbase, fbsh, rbase, rsh, col, colok);
+        } else {
+            // w_Q^(+-b u) = w_256^(+-b u 256/Q) (zeta[0] = 1 for the b = 0 warp), then to shared memory at q' = u*QB + b
+            gl_t *trow = tile + (size_t)b * NTT_LANES + lane;
+            trow[0] = v[0];
+#pragma unroll
+            for (int u = 1; u < QA; u++) {
+                uint32_t zi = (b * (uint32_t)u) << (8 - LOGQ);
+                if (INV) zi = (256 - zi) & 255;
+                trow[(size_t)u * QB * NTT_LANES] = gl_mul(v[ntt_slot<A, INV>(u)], __ldg(a.zeta + zi));
+            }
+        }
+    }
+    if (B == 0) return;
     __syncthreads();
 
-    // Q-point DIF transform in shared memory, radix 2^step_log[s] per step
-    {
-        uint32_t lg = a.logQ;
-        const gl_t *tw = stw;
-        for (uint32_t s = 0; s < a.nsteps; s++) {
-            const bool last_step = (s + 1 == a.nsteps);
-            switch (a.step_log[s]) {
-            case 4: ntt_tile_step<4, CB>(data, tw, a.logQ, lg, last_step); break;
-            case 3: ntt_tile_step<3, CB>(data, tw, a.logQ, lg, last_step); break;
-            case 2: ntt_tile_step<2, CB>(data, tw, a.logQ, lg, last_step); break;
-            default: ntt_tile_step<1, CB>(data, tw, a.logQ, lg, last_step); break;
-            }
-            tw += 1u << lg;
-            lg -= a.step_log[s];
-            __syncthreads();
-        }
+    // ---- step 2: 2^B-point transforms over b; tile output t = u + QA*w ----
+#pragma unroll 1
+    for (uint32_t u = warp; u < (uint32_t)QA; u += NTT_WARPS) {
+        gl_t v[QB];
+        const gl_t *trow = tile + (size_t)u * QB * NTT_LANES + lane;
+#pragma unroll
+        for (int b = 0; b < QB; b++) v[b] = trow[(size_t)b * NTT_LANES];
+        ntt_dft_regs<B, 0>(v);
+        ntt_store_outputs<B, INV>(a, sl, v, u, QA, p, omul, fptr, fsh, fkind, fbase, fbsh, rbase, rsh, col, colok);
     }
+}
 
-    // scatter: shared position j holds tile output k = digit-reversed(j)
-    if (!colok) return;
-    const uint64_t N = 1ull << a.logN;
-    uint64_t kbase = 0;                                          // natural index contributed by earlier passes
-    if (a.last) {
-        if (a.nprev == 1) kbase = b;
-        else if (a.nprev == 2) kbase = (b >> a.logq_prev1) + ((b & ((1ull << a.logq_prev1) - 1)) << a.logq_prev0);
-    }
-    const uint32_t logNQ = a.logN - a.logQ;
-    for (uint32_t j = threadIdx.x / CB; j < Q; j += blockDim.x / CB) {
-        // j = sum_s u_s * (L_s/Q_s)  ->  k = u_0 + Q_0 u_1 + Q_0 Q_1 u_2 ...
-        uint32_t k = 0, lg = a.logQ, sh = 0;
-        for (uint32_t s = 0; s < a.nsteps; s++) {
-            lg -= a.step_log[s];
-            const uint32_t u = (j >> lg) & ((1u << a.step_log[s]) - 1);
-            k |= u << sh;
-            sh += a.step_log[s];
-        }
-        gl_t x = data[ntt_phys(j) * CB + c];
-        if (!a.last) {
-            // w_L^(p k) = w_N^(p k N/L)
-            const uint64_t e = ((p * k) << (a.logN - a.logL)) & (N - 1);
-            if (e) x = gl_mul(x, ntt_tw2(a.tw_lo, a.tw_hi, e));
-            const uint64_t row = (b << a.logL) + ((uint64_t)k << logS) + p;
-            a.out[row * a.out_pitch + a.out_col0 + col] = x;
-        } else {
-            uint64_t K = kbase + ((uint64_t)k << logNQ);
-            if (a.inverse) {
-                K = (N - K) & (N - 1);
-                x = gl_mul(x, a.extend ? ntt_tw2(a.sc_lo, a.sc_hi, K) : a.ninv);
-            }
-            a.out[K * a.out_pitch + a.out_col0 + col] = gl_canon(x);
-        }
+// size-1 "transform": canonical copy
+__global__ void k_ntt_copy_canon(gl_t *out, uint64_t out_pitch, const gl_t *in, uint64_t in_pitch, uint64_t nrows, uint64_t ncols)
+{
+    const uint64_t total = nrows * ncols;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / ncols, c = i % ncols;
+        out[r * out_pitch + c] = gl_canon(in[r * in_pitch + c]);
     }
 }
 
@@ -226,12 +295,28 @@ __global__ void k_ntt_pow_table(gl_t *out, gl_t c, gl_t g, uint64_t mul, uint64_
     if (i >= n) return;
     out[i] = gl_canon(gl_mul(c, gl_pow(g, i * mul)));
 }
-// step table for a sub-transform of length 2^logLs split by radix 2^logQs: out[u*stride + p] = w_Ls^(p u)
-__global__ void k_ntt_step_table(gl_t *out, uint32_t logLs, uint32_t logQs)
+// pass table: out[p*Q + i] = g^(p*i), p < S, i < Q   (g = w_L or its inverse)
+__global__ void k_ntt_pass_table(gl_t *out, gl_t g, uint32_t logQ, uint64_t n)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (1u << logLs)) return;
-    const uint32_t logStride = logLs - logQs;
-    const uint32_t u = i >> logStride, p = i & ((1u << logStride) - 1);
-    out[i] = gl_canon(gl_pow(gl_root_of_unity(logLs), (uint64_t)u * p));
+    uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    const uint64_t p = idx >> logQ, i = idx & ((1ull << logQ) - 1);
+    out[idx] = gl_canon(gl_pow(g, p * i));
+}
+// scale table in the storage order of a DIF transform with tile sizes lg[0..npass): position
+// (k_0, ..., k_(n-1)) (k_0 most significant) holds coefficient j = k_0 + Q_0 k_1 + Q_0 Q_1 k_2 + ...
+struct NttPlanLogs { uint32_t npass, lg[NTT_MAX_PASSES]; };
+__global__ void k_ntt_scale_table(gl_t *out, gl_t c, gl_t g, NttPlanLogs pl, uint64_t n)
+{
+    uint64_t pos = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    uint64_t rem = pos, j = 0;
+    uint32_t sh = 0;
+    for (uint32_t i = 0; i < pl.npass; i++) sh += pl.lg[i];
+    for (int i = (int)pl.npass - 1; i >= 0; i--) {
+        sh -= pl.lg[i];
+        j |= (rem & ((1ull << pl.lg[i]) - 1)) << sh;
+        rem >>= pl.lg[i];
+    }
+    out[pos] = gl_canon(gl_mul(c, gl_pow(g, j)));
 }
