@@ -1,0 +1,19 @@
+#!/bin/bash
+# GPU call: parity tests, headline bench, ncu launch list (full size) and two --set full captures.
+mkdir -p gpurun_out
+nvidia-smi --query-gpu=name,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
+free -g > gpurun_out/host.txt; nproc >> gpurun_out/host.txt; lscpu | head -20 >> gpurun_out/host.txt
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+tail -c 3000 gpurun_out/bench.json
+B="python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline --no-verify"
+$B > gpurun_out/plain_full.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_full.csv $B > gpurun_out/ncu_full.log 2>&1
+echo "ncu list rc=$?"
+$B --log-rows 18 > gpurun_out/plain_leaf.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_linear_hash -s 1 -c 1 -o gpurun_out/prof_leaf $B --log-rows 18 > gpurun_out/ncu_leaf.log 2>&1
+echo "ncu leaf rc=$?"
+$B --cols 64 > gpurun_out/plain_ntt.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_ntt_pass -s 6 -c 6 -o gpurun_out/prof_ntt $B --cols 64 > gpurun_out/ncu_ntt.log 2>&1
+echo "ncu ntt rc=$?"
+ls -la gpurun_out
