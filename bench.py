@@ -344,6 +344,10 @@ def main_ours(args):
                 e2e = run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c0, w, barrier)
             except Exception as ex:                                     # keep the device-resident measurement
                 e2e = {"value": None, "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0, "note": "failed: %r" % (ex,)}
+        if e2e and e2e.get("root") is not None and rank == 0:
+            e2e["root_equals_device_path"] = e2e.pop("root") == result["root"]
+        elif e2e:
+            e2e.pop("root", None)
         result["e2e"] = e2e
 
     if rank == 0:
@@ -458,8 +462,9 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
         step()
     barrier()
     t0 = time.perf_counter()
+    root = None
     for _ in range(K):
-        step()
+        root = step()
     barrier()
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
@@ -470,7 +475,9 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
             ctx.host_free(p)
     return {"value": n * C / sec / 1e6, "unit": "Melem/s", "ms_per_step": sec * 1e3,
             "h2d_bytes_per_step": 8 * n * C, "d2h_bytes_per_step": (8 * n_ext * C if full else 0) + tree_bytes + 32,
-            "note": note, "pinned": True}
+            "note": note, "pinned": True,
+            "root": [int(x) for x in np.asarray(root).view(np.uint64)] if (root is not None and not hasattr(root, "cpu")) else
+                    ([int(x) for x in root.cpu().numpy().view(np.uint64)] if root is not None else None)}
 
 
 def main():

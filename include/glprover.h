@@ -84,6 +84,12 @@ uint64_t glp_root(uint32_t domain_pow, uint64_t idx);
 int glp_hash_full_result(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n);
 /* linear_hash (poseidon_goldilocks.cpp:229-265) of every row: out[i*4..+4) = linear_hash(in[i*pitch..+ncols)). */
 int glp_linear_hash_rows(glp_ctx *ctx, uint64_t *out4, const uint64_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows);
+/* The same sponge one column block at a time (poseidon_goldilocks.cpp:240-262 is a loop over 8-word blocks whose
+ * only carried state is the 4-word capacity = the previous output): absorbs in[i*pitch..+ncols) into state4[i*4..+4).
+ * first != 0 starts a row (capacity zero; a whole row of <= 4 words is copied, :234-239); every block but a row's last
+ * must be a multiple of 8 columns.  After the last block state4 holds linear_hash of the whole row.  This is what
+ * lets glp_commit hash column blocks while later blocks are still being uploaded and extended. */
+int glp_linear_hash_absorb(glp_ctx *ctx, uint64_t *state4, const uint64_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int first);
 /* merkletree / merkletree_avx / merkletree_avx512 (poseidon_goldilocks.cpp:266-301, :484-520):
  * tree = (2*nrows-1)*4 words, level-major, root last.  A row is ncols*dim words.  nrows must be a power of
  * two (the reference reads a neighbour's node otherwise; every caller passes powers of two). */
@@ -101,7 +107,8 @@ int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source
 /* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
  * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip
  * in between.  out_ext and tree may be NULL when the caller only needs the root (they are then kept in
- * device scratch).  With host pointers the column blocks are streamed through pinned staging buffers. */
+ * device scratch).  With a host `in` the commit is a pipeline over column blocks (GLP_STREAM_COLS columns, default 64):
+ * upload of block k+1, LDE + sponge absorption of block k and download of block k-1 overlap on three streams. */
 int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
                uint64_t n, uint64_t n_ext, uint64_t ncols);
 

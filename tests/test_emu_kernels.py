@@ -112,6 +112,51 @@ def test_commit_host_and_device(ectx3, oracle, fixtures):
     check_equal(proof, fixtures["commit_64x9_proof_77"])
 
 
+def check_absorb(ctx, oracle, rng):
+    """linear_hash one column block at a time == linear_hash of the whole row (sponge continuation)"""
+    for ncols, cuts in [(37, [8, 24]), (64, [32]), (20, [16]), (9, [8]), (3, []), (660, [64, 128, 640])]:
+        a = edge_matrix(rng, 6, ncols)
+        want = np.stack([oracle.linear_hash(a[i]) for i in range(a.shape[0])])
+        state = np.full((a.shape[0], 4), 0xDEADBEEF, dtype=np.uint64)       # garbage: must be ignored when first
+        lo = 0
+        for hi in cuts + [ncols]:
+            blk = np.ascontiguousarray(a[:, lo:hi])
+            ctx.linear_hash_absorb(state, blk, hi - lo, hi - lo, a.shape[0], lo == 0)
+            lo = hi
+        check_equal(state, want, "absorb %d cols cut at %s" % (ncols, cuts))
+    # pitched view of the full matrix, device-resident state
+    a = edge_matrix(rng, 5, 29)
+    da, ds = ctx.to_device(a), ctx.device_alloc(5 * 4 * 8)
+    ctx.linear_hash_absorb(ds, da, 16, 29, 5, True)
+    ctx.linear_hash_absorb(ds, da + 16 * 8, 13, 29, 5, False)
+    check_equal(ctx.to_host(ds, (5, 4)), np.stack([oracle.linear_hash(a[i]) for i in range(5)]), "pitched absorb")
+    ctx.device_free(da)
+    ctx.device_free(ds)
+
+
+def test_linear_hash_absorb(ectx, oracle, rng):
+    check_absorb(ectx, oracle, rng)
+
+
+def test_commit_streamed_variants(ectx3, oracle, rng):
+    """host-pointer commit = pipeline over column blocks: root only, extension only, output aliasing the input"""
+    a = edge_matrix(rng, 64, 21)
+    want_ext = oracle.extend_pol(a, 128)
+    want_tree = oracle.merkletree(want_ext)
+    ectx3.set_scratch_limit(1)                                  # smallest blocks: 8 columns -> 3 blocks
+    try:
+        check_equal(ectx3.commit(None, None, a, 64, 128, 21), want_tree[-4:], "root only")
+        buf = np.zeros((128, 21), dtype=np.uint64)
+        buf.reshape(-1)[: a.size] = a.reshape(-1)
+        tree = np.zeros(tree_words(128), dtype=np.uint64)
+        ectx3.commit(buf, tree, buf, 64, 128, 21)               # in place, as Starks does with p_cm1_2ns when buffers overlap
+        check_equal(buf, want_ext, "aliased ext")
+        check_equal(tree, want_tree, "aliased tree")
+        check_equal(run_extend(ectx3, a, 128), want_ext, "extension only")
+    finally:
+        ectx3.set_scratch_limit(0)
+
+
 def test_argument_errors(ectx):
     from xlayer_prover_b200._capi import GLP_E_ARG, GLP_E_DOMAIN, GlpError
     a = np.zeros((12, 2), dtype=np.uint64)

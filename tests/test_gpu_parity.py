@@ -286,6 +286,23 @@ def test_merkletreegl_vs_reference_class(ctx, reference, rng):
         check_equal(mt.getGroupProof(np.zeros(21 + 4 * psize, dtype=np.uint64), idx), gp(idx), "proof %d" % idx)
 
 
+def test_linear_hash_absorb(ctx, oracle, rng):
+    from test_emu_kernels import check_absorb
+    check_absorb(ctx, oracle, rng)
+
+
+def test_commit_streamed_default_blocks(ctx, oracle, rng):
+    """default 64-column pipeline blocks: 3 blocks (64 + 64 + 9), extension + tree + root, and root only"""
+    a = edge_matrix(rng, 1 << 11, 137)
+    check_commit(ctx, oracle, a, 1 << 12)
+    want = oracle.merkletree(oracle.extend_pol(a, 1 << 12))
+    check_equal(ctx.commit(None, None, a, 1 << 11, 1 << 12, 137), want[-4:], "root only")
+    buf = np.zeros((1 << 12, 137), dtype=np.uint64)
+    buf.reshape(-1)[: a.size] = a.reshape(-1)
+    ctx.commit(buf, None, buf, 1 << 11, 1 << 12, 137)
+    check_equal(buf, oracle.extend_pol(a, 1 << 12), "aliased host extension")
+
+
 def test_commit_streamed_host_path(ctx, oracle, rng):
     a = edge_matrix(rng, 1 << 12, 37)
     ctx.set_scratch_limit(((1 << 13) + (1 << 12)) * 8 * 8 * 2)      # 8-column blocks -> 5 streamed blocks

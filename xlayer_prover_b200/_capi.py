@@ -40,6 +40,7 @@ SIGNATURES = {
     "glp_root": (u64, [u32, u64]),
     "glp_hash_full_result": (i32, [vp, vp, vp, u64]),
     "glp_linear_hash_rows": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_linear_hash_absorb": (i32, [vp, vp, vp, u64, u64, u64, i32]),
     "glp_merkletree": (i32, [vp, vp, vp, u64, u64, u64]),
     "glp_merkle_levels": (i32, [vp, vp, u64]),
     "glp_tree_num_elements": (u64, [u64]),
@@ -186,6 +187,9 @@ class Context:
 
     def linear_hash_rows(self, out4, inp, ncols, pitch, nrows):
         self.lib.check(self.lib.glp_linear_hash_rows(self.h, ptr_of(out4), ptr_of(inp), ncols, pitch, nrows))
+
+    def linear_hash_absorb(self, state4, inp, ncols, pitch, nrows, first):
+        self.lib.check(self.lib.glp_linear_hash_absorb(self.h, ptr_of(state4), ptr_of(inp), ncols, pitch, nrows, int(first)))
 
     def merkletree(self, tree, inp, ncols, nrows, dim=1):
         self.lib.check(self.lib.glp_merkletree(self.h, ptr_of(tree), ptr_of(inp), ncols, nrows, dim))

@@ -49,8 +49,10 @@ struct glp_ctx {
     cudaStream_t copy_stream[2] = {nullptr, nullptr};
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
+    uint64_t stream_cols = 64;               // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
+    bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
     bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
     std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
     std::map<uint32_t, TwoLevel> sc_tabs;    // shift^j / N, by logN
@@ -146,6 +148,10 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_pass_tables = npt && atoi(npt) != 0;
     const char *nfl = getenv("GLP_NTT_NO_FUSED_LDE");
     ctx->no_fused_lde = nfl && atoi(nfl) != 0;
+    const char *tr = getenv("GLP_TRACE");
+    ctx->trace = tr && atoi(tr) != 0;
+    const char *sc = getenv("GLP_STREAM_COLS");
+    if (sc && atoi(sc) >= 8) ctx->stream_cols = (uint64_t)(atoi(sc) / 8) * 8;
     *out = ctx;
     return GLP_OK;
 }
@@ -732,13 +738,13 @@ extern "C" int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, u
 // ------------------------------------------------------------------------------------------------
 extern "C" uint64_t glp_tree_num_elements(uint64_t nrows) { return nrows ? (2 * nrows - 1) * 4 : 0; }
 
-static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows)
+static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows, const gl_t *cap_in = nullptr)
 {
     if (!nrows) return GLP_OK;
     const int vec16 = (pitch % 2 == 0) && (((uintptr_t)in) % 16 == 0);
     const uint64_t nblk = (nrows + POS_LEAF_BLOCK - 1) / POS_LEAF_BLOCK;
     if (nblk > 0x7FFFFFFFull) return fail(GLP_E_ARG, "too many rows");
-    LAUNCH_FLAT(ctx, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>, (unsigned)nblk, POS_LEAF_BLOCK, out4, in, ncols, pitch, nrows, vec16);
+    LAUNCH_FLAT(ctx, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>, (unsigned)nblk, POS_LEAF_BLOCK, out4, in, ncols, pitch, nrows, vec16, cap_in);
     CU(cudaGetLastError());
     return GLP_OK;
 }
@@ -801,6 +807,30 @@ extern "C" int glp_linear_hash_rows(glp_ctx *ctx, uint64_t *out4, const uint64_t
     if (!out_dev) { GLP(ensure(ctx, ctx->tmp_out, 4 * nrows * sizeof(gl_t))); dout = (gl_t *)ctx->tmp_out.p; }
     GLP(dev_leaf_hash(ctx, dout, din, ncols, pitch, nrows));
     if (!out_dev) CU(cudaMemcpyAsync(out4, dout, 4 * nrows * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_linear_hash_absorb(glp_ctx *ctx, uint64_t *state4, const uint64_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows,
+                                      int first)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!nrows) return GLP_OK;
+    if (!state4 || (!in && ncols)) return fail(GLP_E_ARG, "glp_linear_hash_absorb: NULL pointer");
+    if (pitch < ncols) return fail(GLP_E_ARG, "glp_linear_hash_absorb: pitch smaller than ncols");
+    if (!first && ncols == 0) return GLP_OK;                        // nothing to absorb
+    CU(cudaSetDevice(ctx->device));
+    const gl_t *din = (const gl_t *)in;
+    if (ncols) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)(nrows - 1) * pitch + ncols, &din));
+    const bool st_dev = on_device(state4);
+    gl_t *dst = (gl_t *)state4;
+    if (!st_dev) {
+        GLP(ensure(ctx, ctx->tmp_out, 4 * nrows * sizeof(gl_t)));
+        dst = (gl_t *)ctx->tmp_out.p;
+        if (!first) CU(cudaMemcpyAsync(dst, state4, 4 * nrows * sizeof(gl_t), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    GLP(dev_leaf_hash(ctx, dst, din, ncols, pitch, nrows, first ? nullptr : dst));
+    if (!st_dev) CU(cudaMemcpyAsync(state4, dst, 4 * nrows * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return GLP_OK;
 }
@@ -876,6 +906,113 @@ extern "C" int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint6
 // ------------------------------------------------------------------------------------------------
 // fused commit
 // ------------------------------------------------------------------------------------------------
+// Host input: the commit as a software pipeline over column blocks of `w` columns (a multiple of 8, so every
+// sponge block of the leaf hash has one owner).  Per block k:
+//     copy stream 0 : upload block k (strided 2-D copy out of the row-major host matrix)
+//     compute stream: LDE of block k  ->  absorb block k into every row's sponge (the leaf array IS the sponge state)
+//     copy stream 1 : download block k of the extension (strided 2-D copy into the row-major host matrix)
+// so H2D, arithmetic and D2H of different blocks overlap and the full extended matrix never has to exist on the
+// device (2 x (N + N_ext) x w words of staging instead).  After the last block the leaf array holds the leaf
+// hashes and the level loop runs in place.  out_ext may alias in (same pitch): block k's download only overwrites
+// the columns block k's upload has already read.
+static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64_t *tree, bool tree_dev, gl_t *dtree, uint64_t root[4],
+                           const uint64_t *in, uint64_t n, uint64_t n_ext, uint64_t ncols)
+{
+    const bool want_tree = dtree != nullptr;
+    const bool want_ext = out_ext != nullptr;
+    const size_t tree_words = glp_tree_num_elements(n_ext);
+    const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
+    // block width: GLP_STREAM_COLS (default 64), shrunk to fit the scratch budget
+    uint64_t w = ctx->stream_cols;
+    {
+        size_t f = 0, t = 0;
+        if (cudaMemGetInfo(&f, &t) != cudaSuccess) { cudaGetLastError(); f = (size_t)1 << 30; }
+        uint64_t budget = (uint64_t)f + ctx->tmp_in.bytes + ctx->tmp_out.bytes + ctx->s2.bytes;
+        budget = budget / 10 * 8;
+        if (ctx->scratch_limit && ctx->scratch_limit < budget) budget = ctx->scratch_limit;
+        const uint64_t per_col = 8 * (2 * n + (ext_dev ? 0 : 2 * n_ext) + n);
+        while (w > 8 && w * per_col > budget) w -= 8;
+    }
+    if (w > ncols) w = ncols;
+    const uint64_t nblocks = (ncols + w - 1) / w;
+    GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * w * sizeof(gl_t)));
+    if (!ext_dev) GLP(ensure(ctx, ctx->tmp_out, 2 * (size_t)n_ext * w * sizeof(gl_t)));
+    gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
+    gl_t *extb[2] = {(gl_t *)ctx->tmp_out.p, ext_dev ? nullptr : (gl_t *)ctx->tmp_out.p + (size_t)n_ext * w};
+    std::vector<cudaEvent_t> up(nblocks), lde_done(nblocks), down(nblocks), hashed(nblocks);
+    const unsigned evflags = ctx->trace ? cudaEventDefault : cudaEventDisableTiming;     // GLP_TRACE=1: print the pipeline's timeline
+    for (uint64_t k = 0; k < nblocks; k++) {
+        CU(cudaEventCreateWithFlags(&up[k], evflags));
+        CU(cudaEventCreateWithFlags(&lde_done[k], evflags));
+        CU(cudaEventCreateWithFlags(&down[k], evflags));
+        CU(cudaEventCreateWithFlags(&hashed[k], evflags));
+    }
+    cudaEvent_t start;
+    CU(cudaEventCreateWithFlags(&start, evflags));
+    CU(cudaEventRecord(start, ctx->stream));                      // the copy streams must not run ahead of earlier work on the caller's stream
+    CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
+    CU(cudaStreamWaitEvent(ctx->copy_stream[1], start, 0));
+    auto width = [&](uint64_t k) { return (uint32_t)((ncols - k * w < w) ? ncols - k * w : w); };
+    auto upload = [&](uint64_t k) -> int {
+        if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
+        CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)width(k) * 8, in + k * w, (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
+                             ctx->copy_stream[0]));
+        CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
+        return GLP_OK;
+    };
+    GLP(upload(0));
+    if (nblocks > 1) GLP(upload(1));
+    for (uint64_t k = 0; k < nblocks; k++) {
+        const uint64_t c0 = k * w;
+        const uint32_t wk = width(k);
+        gl_t *eb = ext_dev ? (gl_t *)out_ext + c0 : extb[k & 1];
+        const uint64_t eb_pitch = ext_dev ? ncols : wk;
+        CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
+        if (!ext_dev && want_ext && k >= 2) CU(cudaStreamWaitEvent(ctx->stream, down[k - 2], 0));   // extension buffer still being downloaded
+        GLP(lde_block(ctx, logN, logE, stage[k & 1], wk, eb, eb_pitch, wk));
+        CU(cudaEventRecord(lde_done[k], ctx->stream));
+        if (k + 2 < nblocks) GLP(upload(k + 2));
+        if (want_ext && !ext_dev) {
+            CU(cudaStreamWaitEvent(ctx->copy_stream[1], lde_done[k], 0));
+            CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)ncols * 8, eb, (size_t)wk * 8, (size_t)wk * 8, n_ext, cudaMemcpyDeviceToHost,
+                                 ctx->copy_stream[1]));
+            CU(cudaEventRecord(down[k], ctx->copy_stream[1]));
+        }
+        if (want_tree) {
+            ProfScope ps(ctx, 2);
+            GLP(dev_leaf_hash(ctx, dtree, eb, wk, eb_pitch, n_ext, k == 0 ? nullptr : dtree));
+        }
+        if (ctx->trace) CU(cudaEventRecord(hashed[k], ctx->stream));
+    }
+    if (want_tree) {
+        {
+            ProfScope ps(ctx, 3);
+            GLP(dev_tree_levels(ctx, dtree, n_ext));
+        }
+        if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    }
+    cudaError_t e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->copy_stream[0]),
+                e2 = cudaStreamSynchronize(ctx->copy_stream[1]);
+    if (ctx->trace && e0 == cudaSuccess && e1 == cudaSuccess && e2 == cudaSuccess) {
+        fprintf(stderr, "[glp trace] streamed commit: %llu blocks of %llu columns; ms since start: block  uploaded  extended  hashed  downloaded\n",
+                (unsigned long long)nblocks, (unsigned long long)w);
+        for (uint64_t k = 0; k < nblocks; k++) {
+            float t[4] = {-1, -1, -1, -1};
+            cudaEventElapsedTime(&t[0], start, up[k]);
+            cudaEventElapsedTime(&t[1], start, lde_done[k]);
+            if (want_tree) cudaEventElapsedTime(&t[2], start, hashed[k]);
+            if (want_ext && !ext_dev) cudaEventElapsedTime(&t[3], start, down[k]);
+            fprintf(stderr, "[glp trace] %3llu %9.1f %9.1f %9.1f %9.1f\n", (unsigned long long)k, t[0], t[1], t[2], t[3]);
+        }
+        cudaGetLastError();
+    }
+    for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(lde_done[k]); cudaEventDestroy(down[k]); cudaEventDestroy(hashed[k]); }
+    cudaEventDestroy(start);
+    CU(e0); CU(e1); CU(e2);
+    return GLP_OK;
+}
+
 extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in, uint64_t n,
                           uint64_t n_ext, uint64_t ncols)
 {
@@ -889,66 +1026,16 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
     const size_t in_words = (size_t)n * ncols, ext_words = (size_t)n_ext * ncols, tree_words = glp_tree_num_elements(n_ext);
     const bool in_dev = on_device(in), ext_dev = on_device(out_ext), tree_dev = on_device(tree);
 
-    // extended matrix lives on the device for the Merkle stage whatever the caller's pointers are
-    gl_t *dext = (gl_t *)out_ext;
-    if (!ext_dev) { GLP(ensure(ctx, ctx->ext, ext_words * sizeof(gl_t))); dext = (gl_t *)ctx->ext.p; }
     gl_t *dtree = (gl_t *)tree;
     if (want_tree && !tree_dev) { GLP(ensure(ctx, ctx->nodes, tree_words * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+    if (!in_dev) return commit_streamed(ctx, out_ext, ext_dev, tree, tree_dev, dtree, root, in, n, n_ext, ncols);
 
-    if (in_dev) {
-        GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
-        if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
-    } else {
-        // Host input: stream column blocks.  Block k+1 is uploaded (strided 2-D copy out of the row-major host
-        // matrix) on a copy stream while block k is transformed, and finished blocks of the extension are
-        // downloaded on the other copy stream while later blocks are still being computed.
-        const uint32_t wb = pick_block_cols(ctx, 2 * (n_ext + n), ncols);   // scratch + double-buffered upload
-        GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * wb * sizeof(gl_t)));
-        gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * wb};
-        const uint64_t nblocks = (ncols + wb - 1) / wb;
-        std::vector<cudaEvent_t> up(nblocks), done(nblocks), free_stage(nblocks);
-        for (uint64_t k = 0; k < nblocks; k++) {
-            CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&free_stage[k], cudaEventDisableTiming));
-        }
-        auto upload = [&](uint64_t k) -> int {
-            const uint64_t c0 = k * wb;
-            const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-            if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], free_stage[k - 2], 0));
-            CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)w * 8, in + c0, (size_t)ncols * 8, (size_t)w * 8, n, cudaMemcpyHostToDevice,
-                                 ctx->copy_stream[0]));
-            CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
-            return GLP_OK;
-        };
-        GLP(upload(0));
-        for (uint64_t k = 0; k < nblocks; k++) {
-            const uint64_t c0 = k * wb;
-            const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-            if (k + 1 < nblocks) GLP(upload(k + 1));
-            CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
-            // (the staging buffer is free again once the block's INTT has read it; for simplicity it is released after the block)
-            GLP(lde_block(ctx, ilog2_u64(n), ilog2_u64(n_ext), stage[k & 1], w, dext + c0, ncols, w));
-            CU(cudaEventRecord(free_stage[k], ctx->stream));
-            CU(cudaEventRecord(done[k], ctx->stream));
-            if (out_ext && !ext_dev) {
-                CU(cudaStreamWaitEvent(ctx->copy_stream[1], done[k], 0));
-                CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)ncols * 8, dext + c0, (size_t)ncols * 8, (size_t)w * 8, n_ext,
-                                     cudaMemcpyDeviceToHost, ctx->copy_stream[1]));
-            }
-        }
-        for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(free_stage[k]); }
-        // `done` events are destroyed after the final sync below
-        if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
-        if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
-        if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
-        CU(cudaStreamSynchronize(ctx->stream));
-        CU(cudaStreamSynchronize(ctx->copy_stream[0]));
-        CU(cudaStreamSynchronize(ctx->copy_stream[1]));
-        for (uint64_t k = 0; k < nblocks; k++) cudaEventDestroy(done[k]);
-        (void)in_words;
-        return GLP_OK;
-    }
+    // device-resident input: the extended matrix lives on the device for the Merkle stage
+    gl_t *dext = (gl_t *)out_ext;
+    if (!ext_dev) { GLP(ensure(ctx, ctx->ext, ext_words * sizeof(gl_t))); dext = (gl_t *)ctx->ext.p; }
+    GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
+    if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    (void)in_words;
     if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
     if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));

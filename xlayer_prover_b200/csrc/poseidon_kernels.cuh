@@ -41,11 +41,14 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 }
 
 // out[row*4 .. +4) = linear_hash(in[row*pitch .. +ncols))
+// cap_in != NULL continues a sponge: the capacity starts from cap_in[row*4 .. +4) (the first four outputs of the
+// previous block's last permutation, :247-250) instead of zero, so a row can be absorbed one column block at a time
+// (every block but the last a multiple of 8 columns); cap_in may alias out.
 // LOCKSTEP: every thread of the CTA runs the same number of permutations (rows past the end are clamped to the
 // last row and simply not stored), so the per-round barriers inside pos_permute_t are reached by all.
 template <bool LOCKSTEP>
 __global__ void __launch_bounds__(POS_LEAF_BLOCK)
-k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16)
+k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in)
 {
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = row < nrows;
@@ -55,7 +58,7 @@ k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t
     }
     const gl_t *p = in + row * pitch;
     gl_t *o = out + row * 4;
-    if (ncols <= POS_CAP) {                       // size <= CAPACITY: copy and zero-pad, no hashing (:234-239)
+    if (ncols <= POS_CAP && !cap_in) {            // size <= CAPACITY: copy and zero-pad, no hashing (:234-239)
         if (live) {
 #pragma unroll
             for (int i = 0; i < 4; i++) o[i] = (uint64_t)i < ncols ? gl_canon(p[i]) : 0;
@@ -67,7 +70,7 @@ k_linear_hash_rows(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t
     uint64_t nblk = (ncols + 7) / 8;
     pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16 != 0);
 #pragma unroll
-    for (int i = 8; i < 12; i++) x[i] = 0;        // capacity starts at zero (:243-246)
+    for (int i = 8; i < 12; i++) x[i] = cap_in ? cap_in[row * 4 + (i - 8)] : 0;   // capacity starts at zero (:243-246)
 #pragma unroll 1
     for (uint64_t b = 0; b < nblk; b++) {
 #pragma unroll
