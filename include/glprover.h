@@ -107,7 +107,7 @@ int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source
 /* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
  * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip
  * in between.  out_ext and tree may be NULL when the caller only needs the root (they are then kept in
- * device scratch).  With a host `in` the commit is a pipeline over column blocks (GLP_STREAM_COLS columns, default 64):
+ * device scratch).  With a host `in` the commit is a pipeline over column blocks (GLP_STREAM_COLS columns, default 96):
  * upload of block k+1, LDE + sponge absorption of block k and download of block k-1 overlap on three streams. */
 int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
                uint64_t n, uint64_t n_ext, uint64_t ncols);
@@ -119,7 +119,8 @@ int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, 
 /* out[0] = sum of all words mod p, out[1] = sum of word_i * (i+1) mod p  (order-sensitive checksum) */
 int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2]);
 /* exercises every device field primitive (PTX paths) on n pseudo-random + edge operands and returns the
- * results for the host to compare against the oracle: out[5*i..] = add, sub, mul, mul_pow2(a, b%96), canon */
+ * results for the host to compare against the oracle:
+ * out[8*i..] = a+b, a-b, a*b, a*2^(b%96), canon(a), a^2, b^7, add_c(a, canon(b)) */
 int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_t *b, uint64_t n, uint64_t *out);
 
 /* ---- measurement hooks (bench.py) ---- */

@@ -157,6 +157,18 @@ def test_commit_streamed_variants(ectx3, oracle, rng):
         ectx3.set_scratch_limit(0)
 
 
+def test_commit_streamed_short_first_block(emu_lib, oracle, rng):
+    """GLP_STREAM_COLS=40 at 100 columns: blocks of 32 (short first), 40, 28"""
+    os.environ["GLP_STREAM_COLS"] = "40"
+    try:
+        c = make_ctx(emu_lib)
+    finally:
+        os.environ.pop("GLP_STREAM_COLS", None)
+    a = edge_matrix(rng, 16, 100)
+    check_commit(c, oracle, a, 32)
+    c.close()
+
+
 def test_argument_errors(ectx):
     from xlayer_prover_b200._capi import GLP_E_ARG, GLP_E_DOMAIN, GlpError
     a = np.zeros((12, 2), dtype=np.uint64)

@@ -40,7 +40,8 @@ def test_field_primitives(ctx, rng):
     got = ctx.field_selftest(a, b)
     ai = [int(x) for x in a]
     bi = [int(x) for x in b]
-    want = np.array([[(x + y) % P, (x - y) % P, (x * y) % P, (x * pow(2, y % 96, P)) % P, x % P] for x, y in zip(ai, bi)],
+    want = np.array([[(x + y) % P, (x - y) % P, (x * y) % P, (x * pow(2, y % 96, P)) % P, x % P, x * x % P, pow(y, 7, P), (x + y) % P]
+                     for x, y in zip(ai, bi)],
                     dtype=np.uint64)
     check_equal(got, want, "field selftest")
 
@@ -292,14 +293,15 @@ def test_linear_hash_absorb(ctx, oracle, rng):
 
 
 def test_commit_streamed_default_blocks(ctx, oracle, rng):
-    """default 64-column pipeline blocks: 3 blocks (64 + 64 + 9), extension + tree + root, and root only"""
-    a = edge_matrix(rng, 1 << 11, 137)
+    """default pipeline blocks at 300 columns: 32 (short first block) + 96 + 88 + 84; extension + tree + root, root only,
+    and the extension written over the input"""
+    a = edge_matrix(rng, 1 << 11, 300)
     check_commit(ctx, oracle, a, 1 << 12)
     want = oracle.merkletree(oracle.extend_pol(a, 1 << 12))
-    check_equal(ctx.commit(None, None, a, 1 << 11, 1 << 12, 137), want[-4:], "root only")
-    buf = np.zeros((1 << 12, 137), dtype=np.uint64)
+    check_equal(ctx.commit(None, None, a, 1 << 11, 1 << 12, 300), want[-4:], "root only")
+    buf = np.zeros((1 << 12, 300), dtype=np.uint64)
     buf.reshape(-1)[: a.size] = a.reshape(-1)
-    ctx.commit(buf, None, buf, 1 << 11, 1 << 12, 137)
+    ctx.commit(buf, None, buf, 1 << 11, 1 << 12, 300)
     check_equal(buf, oracle.extend_pol(a, 1 << 12), "aliased host extension")
 
 

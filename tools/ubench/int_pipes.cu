@@ -65,6 +65,16 @@ __global__ void __launch_bounds__(256) k_pipe(uint64_t *sink, uint32_t iters, lo
                     asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(f) : "f"(__uint_as_float(b)), "f"(__uint_as_float(a)));
                     m[i] = __float_as_uint(f);
                 }
+                if (MODE == 14 || MODE == 15 || MODE == 16) {  // DFMA alone / DFMA + IMAD.WIDE / DFMA + IMAD.WIDE + IADD3
+                    double dd = __longlong_as_double((long long)w[i]);
+                    asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(dd) : "d"(__longlong_as_double(0x3FF0000000000001LL)), "d"(__longlong_as_double(0x3FF0000000000003LL)));
+                    w[i] = (uint64_t)__double_as_longlong(dd);
+                    if (MODE >= 15) asm volatile("{ mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.u32 %1, %2, %3, %1; }" : "+r"(m[i]), "+r"(s[i]) : "r"(a), "r"(b));
+                    if (MODE == 16) asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(m[(i + 1) % CHAINS]) : "r"(s[(i + 3) % CHAINS]), "r"(a));
+                }
+                if (MODE == 17) {  // IMAD.WIDE via mad.lo.cc/madc.hi (register-pair accumulate), alone
+                    asm volatile("{ mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.u32 %1, %2, %3, %1; }" : "+r"(m[i]), "+r"(s[i]) : "r"(a), "r"(b));
+                }
                 if (MODE == 13) {  // IMAD.WIDE (1) + IADD3 (1) + LOP3 (1)
                     asm volatile("{ .reg .u32 l,h; mov.b64 {l,h}, %1; mad.wide.u32 %0, l, %2, %0; }" : "+l"(w[i]) : "l"(w[(i + 3) % CHAINS]), "r"(b));
                     asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(s[i]) : "r"(s[(i + 3) % CHAINS]), "r"(a));
@@ -83,8 +93,8 @@ __global__ void __launch_bounds__(256) k_pipe(uint64_t *sink, uint32_t iters, lo
 
 static const char *NAMES[] = {"IMAD.LO", "IMAD.WIDE", "IMAD.HI", "IADD3", "IMAD.WIDE+IADD3", "IMAD.WIDE+2*IADD3", "IMAD.LO+IADD3",
                               "add.cc+addc", "mad.lo.cc+madc.hi.cc+addc", "SHF+LOP3", "IMAD.WIDE+IMAD.LO", "IMAD.WIDE(x*1+C)", "FFMA",
-                              "IMAD.WIDE+IADD3+LOP3"};
-static const int OPS[] = {1, 1, 1, 1, 2, 3, 2, 2, 3, 2, 2, 1, 1, 3};
+                              "IMAD.WIDE+IADD3+LOP3", "DFMA", "DFMA+IMAD.WIDE", "DFMA+IMAD.WIDE+IADD3", "IMAD.WIDE(mad.lo.cc/madc.hi)"};
+static const int OPS[] = {1, 1, 1, 1, 2, 3, 2, 2, 3, 2, 2, 1, 1, 3, 1, 2, 3, 1};
 
 template <int MODE>
 static void run(uint64_t *sink, long long *dcyc, int blocks_per_sm)
@@ -117,11 +127,12 @@ int main()
     long long *dcyc;
     cudaMalloc(&sink, 64);
     cudaMalloc(&dcyc, 64);
-    for (int bps : {8, 4, 2}) {
+    for (int bps : {8, 2}) {
         run<0>(sink, dcyc, bps); run<1>(sink, dcyc, bps); run<2>(sink, dcyc, bps); run<3>(sink, dcyc, bps);
         run<4>(sink, dcyc, bps); run<5>(sink, dcyc, bps); run<6>(sink, dcyc, bps); run<7>(sink, dcyc, bps);
         run<8>(sink, dcyc, bps); run<9>(sink, dcyc, bps); run<10>(sink, dcyc, bps); run<11>(sink, dcyc, bps);
         run<12>(sink, dcyc, bps); run<13>(sink, dcyc, bps);
+        run<14>(sink, dcyc, bps); run<15>(sink, dcyc, bps); run<16>(sink, dcyc, bps); run<17>(sink, dcyc, bps);
         printf("\n");
     }
     cudaError_t e = cudaDeviceSynchronize();

@@ -217,7 +217,7 @@ class Context:
     def field_selftest(self, a, b):
         a = np.ascontiguousarray(a, dtype=np.uint64)
         b = np.ascontiguousarray(b, dtype=np.uint64)
-        out = np.zeros((a.size, 5), dtype=np.uint64)
+        out = np.zeros((a.size, 8), dtype=np.uint64)
         self.lib.check(self.lib.glp_field_selftest(self.h, ptr_of(a), ptr_of(b), a.size, ptr_of(out)))
         return out
 

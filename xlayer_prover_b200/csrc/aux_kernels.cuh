@@ -79,16 +79,20 @@ __global__ void k_reverse_permutation(gl_t *dst, const gl_t *src, uint64_t size,
     }
 }
 
+#define GLP_SELFTEST_OUTS 8
 __global__ void k_field_selftest(const gl_t *a, const gl_t *b, uint64_t n, gl_t *out)
 {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const gl_t x = a[i], y = b[i];
-    out[5 * i + 0] = gl_canon(gl_add(x, y));
-    out[5 * i + 1] = gl_canon(gl_sub(x, y));
-    out[5 * i + 2] = gl_canon(gl_mul(x, y));
-    out[5 * i + 3] = gl_canon(gl_mul_pow2(x, (unsigned)(y % 96)));
-    out[5 * i + 4] = gl_canon(x);
+    out[GLP_SELFTEST_OUTS * i + 0] = gl_canon(gl_add(x, y));
+    out[GLP_SELFTEST_OUTS * i + 1] = gl_canon(gl_sub(x, y));
+    out[GLP_SELFTEST_OUTS * i + 2] = gl_canon(gl_mul(x, y));
+    out[GLP_SELFTEST_OUTS * i + 3] = gl_canon(gl_mul_pow2(x, (unsigned)(y % 96)));
+    out[GLP_SELFTEST_OUTS * i + 4] = gl_canon(x);
+    out[GLP_SELFTEST_OUTS * i + 5] = gl_canon(gl_sqr(x));
+    out[GLP_SELFTEST_OUTS * i + 6] = gl_canon(gl_pow7(y));
+    out[GLP_SELFTEST_OUTS * i + 7] = gl_canon(gl_add_c(x, gl_canon(y)));
 }
 
 // ---- integer-pipe peak micro-benchmarks ("the IMAD peak must be measured on the box") ----

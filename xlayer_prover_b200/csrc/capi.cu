@@ -49,7 +49,7 @@ struct glp_ctx {
     cudaStream_t copy_stream[2] = {nullptr, nullptr};
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
-    uint64_t stream_cols = 64;               // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
+    uint64_t stream_cols = 96;               // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
@@ -922,7 +922,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     const bool want_ext = out_ext != nullptr;
     const size_t tree_words = glp_tree_num_elements(n_ext);
     const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
-    // block width: GLP_STREAM_COLS (default 64), shrunk to fit the scratch budget
+    // block width: GLP_STREAM_COLS (default 96), shrunk to fit the scratch budget
     uint64_t w = ctx->stream_cols;
     {
         size_t f = 0, t = 0;
@@ -933,8 +933,28 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         const uint64_t per_col = 8 * (2 * n + (ext_dev ? 0 : 2 * n_ext) + n);
         while (w > 8 && w * per_col > budget) w -= 8;
     }
-    if (w > ncols) w = ncols;
-    const uint64_t nblocks = (ncols + w - 1) / w;
+    // Blocks in units of 8 columns.  The first block is short (32 columns) so that the GPU starts after a short
+    // upload -- nothing overlaps the first upload; the rest are equal (a short LAST block would only be copied in
+    // short, slow rows: 160-byte rows move at 18 GB/s, 768-byte rows at 46-52 GB/s, profiles/r01_pcie_probe.txt).
+    const uint64_t units = (ncols + 7) / 8;
+    const uint64_t wu = w / 8;                                              // units per full block
+    const uint64_t first = (units > 2 * wu && wu > 4) ? 4 : 0;             // units of the short first block
+    const uint64_t rest = units - first;
+    uint64_t nrest = (rest + wu - 1) / wu;
+    if (nrest < 1) nrest = 1;
+    const uint64_t ub = rest / nrest, extra = rest % nrest;                 // the first `extra` equal blocks get ub+1 units
+    const uint64_t nblocks = nrest + (first ? 1 : 0);
+    w = (ub + (extra ? 1 : 0)) * 8;                                          // widest block: sizes the buffers
+    std::vector<uint64_t> col0(nblocks + 1);
+    col0[0] = 0;
+    for (uint64_t k = 0; k < nblocks; k++) {
+        uint64_t u;
+        if (first && k == 0) u = first;
+        else { const uint64_t kk = k - (first ? 1 : 0); u = ub + (kk < extra ? 1 : 0); }
+        const uint64_t c1 = col0[k] + u * 8;
+        col0[k + 1] = c1 < ncols ? c1 : ncols;
+    }
+    col0[nblocks] = ncols;
     GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * w * sizeof(gl_t)));
     if (!ext_dev) GLP(ensure(ctx, ctx->tmp_out, 2 * (size_t)n_ext * w * sizeof(gl_t)));
     gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
@@ -952,10 +972,10 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     CU(cudaEventRecord(start, ctx->stream));                      // the copy streams must not run ahead of earlier work on the caller's stream
     CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
     CU(cudaStreamWaitEvent(ctx->copy_stream[1], start, 0));
-    auto width = [&](uint64_t k) { return (uint32_t)((ncols - k * w < w) ? ncols - k * w : w); };
+    auto width = [&](uint64_t k) { return (uint32_t)(col0[k + 1] - col0[k]); };
     auto upload = [&](uint64_t k) -> int {
         if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
-        CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)width(k) * 8, in + k * w, (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
+        CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)width(k) * 8, in + col0[k], (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
                              ctx->copy_stream[0]));
         CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
         return GLP_OK;
@@ -963,7 +983,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     GLP(upload(0));
     if (nblocks > 1) GLP(upload(1));
     for (uint64_t k = 0; k < nblocks; k++) {
-        const uint64_t c0 = k * w;
+        const uint64_t c0 = col0[k];
         const uint32_t wk = width(k);
         gl_t *eb = ext_dev ? (gl_t *)out_ext + c0 : extb[k & 1];
         const uint64_t eb_pitch = ext_dev ? ncols : wk;
@@ -1093,12 +1113,12 @@ extern "C" int glp_field_selftest(glp_ctx *ctx, const uint64_t *a, const uint64_
     DevBuf da, db, dout;
     int rc = ensure(ctx, da, n * 8);
     if (rc == GLP_OK) rc = ensure(ctx, db, n * 8);
-    if (rc == GLP_OK) rc = ensure(ctx, dout, 5 * n * 8);
+    if (rc == GLP_OK) rc = ensure(ctx, dout, GLP_SELFTEST_OUTS * n * 8);
     if (rc == GLP_OK) {
         cudaMemcpyAsync(da.p, a, n * 8, cudaMemcpyDefault, ctx->stream);
         cudaMemcpyAsync(db.p, b, n * 8, cudaMemcpyDefault, ctx->stream);
         LAUNCH_FLAT(ctx, k_field_selftest, (unsigned)((n + 127) / 128), 128, (const gl_t *)da.p, (const gl_t *)db.p, n, (gl_t *)dout.p);
-        cudaMemcpyAsync(out, dout.p, 5 * n * 8, cudaMemcpyDefault, ctx->stream);
+        cudaMemcpyAsync(out, dout.p, GLP_SELFTEST_OUTS * n * 8, cudaMemcpyDefault, ctx->stream);
         cudaError_t e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) rc = fail(GLP_E_CUDA, cudaGetErrorString(e));
     }

@@ -39,6 +39,23 @@ typedef unsigned long long gl_t;   // same width as the reference's Goldilocks::
 #define GL_W32 7277203076849721926ULL
 #define GL_SHIFT 7ULL              // coset generator, Goldilocks::SHIFT (goldilocks_base_field.cpp:50)
 
+// (lo1:lo0) += h*EPS with the carry flag left for the following addc, as PTX text (h*EPS = (h << 32) - h).
+//   _ALU: two subtracts + two adds on the ALU pipe -- for the Poseidon kernels, which are bound by the fmaheavy pipe;
+//   _FMA: mad.lo.cc/madc.hi.cc, which ptxas turns into an IMAD.HI (4 fmaheavy cycles) -- for the NTT kernels, which are
+//         bound by the ALU pipe.
+#define GL_PTX_ADD_EPS_MUL_ALU(lo0, lo1, h)                               \
+    "{\n\t.reg .u32 e0,e1;\n\t"                                          \
+    "sub.cc.u32 e0, 0, " h ";\n\t"                                        \
+    "subc.u32 e1, " h ", 0;\n\t"                                          \
+    "add.cc.u32 " lo0 ", " lo0 ", e0;\n\t"                                \
+    "addc.cc.u32 " lo1 ", " lo1 ", e1;\n\t}\n\t"
+#define GL_PTX_ADD_EPS_MUL_FMA(lo0, lo1, h)                               \
+    "mad.lo.cc.u32 " lo0 ", " h ", 0xffffffff, " lo0 ";\n\t"              \
+    "madc.hi.cc.u32 " lo1 ", " h ", 0xffffffff, " lo1 ";\n\t"
+#ifndef GL_EPS_ALU
+#define GL_EPS_ALU 0          // what plain gl_mul / gl_reduce128 use; the NTT kernels ask for the _FMA form explicitly
+#endif
+
 GL_HD gl_t gl_canon(gl_t a) { return a >= GL_P ? a - GL_P : a; }
 
 // a + b (mod p).  Handles the double wrap the reference handles (two non-canonical operands).
@@ -124,28 +141,32 @@ GL_HD gl_t gl_sub(gl_t a, gl_t b)
 
 GL_HD gl_t gl_neg(gl_t a) { return gl_sub(0, a); }
 
-// fold a 128-bit value hi:lo to 64 bits (mod p)
-GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi)
+// fold a 128-bit value hi:lo to 64 bits (mod p); EPSALU picks the pipe of the p2*EPS term (see above)
+template <bool EPSALU>
+GL_HD gl_t gl_reduce128_t(gl_t lo, gl_t hi)
 {
 #if GL_DEVICE_PTX
     gl_t r;
-    asm("{\n\t"
-        ".reg .u32 p0,p1,p2,p3,m;\n\t"
-        "mov.b64 {p0,p1}, %1;\n\t"
-        "mov.b64 {p2,p3}, %2;\n\t"
-        "sub.cc.u32 p0, p0, p3;\n\t"            // (p1:p0) - p3          [2^96 = -1]
-        "subc.cc.u32 p1, p1, 0;\n\t"
-        "subc.u32 m, 0, 0;\n\t"
-        "sub.cc.u32 p0, p0, m;\n\t"             //   - EPS on borrow
-        "subc.u32 p1, p1, 0;\n\t"
-        "mad.lo.cc.u32 p0, p2, 0xffffffff, p0;\n\t"  // + p2*EPS        [2^64 = EPS]   (one IMAD.WIDE)
-        "madc.hi.cc.u32 p1, p2, 0xffffffff, p1;\n\t"
-        "addc.u32 m, 0, 0;\n\t"                      // + carry*EPS = - carry + (carry << 32)
-        "sub.cc.u32 p0, p0, m;\n\t"
-        "subc.u32 p1, p1, 0;\n\t"
-        "add.u32 p1, p1, m;\n\t"
-        "mov.b64 %0, {p0,p1};\n\t"
-        "}" : "=l"(r) : "l"(lo), "l"(hi));
+#define GL_REDUCE128_PTX(EPSMUL)                                                                       \
+    asm("{\n\t"                                                                                        \
+        ".reg .u32 p0,p1,p2,p3,m;\n\t"                                                                 \
+        "mov.b64 {p0,p1}, %1;\n\t"                                                                     \
+        "mov.b64 {p2,p3}, %2;\n\t"                                                                     \
+        "sub.cc.u32 p0, p0, p3;\n\t" /* (p1:p0) - p3          [2^96 = -1] */                           \
+        "subc.cc.u32 p1, p1, 0;\n\t"                                                                   \
+        "subc.u32 m, 0, 0;\n\t"                                                                        \
+        "sub.cc.u32 p0, p0, m;\n\t" /*   - EPS on borrow */                                            \
+        "subc.u32 p1, p1, 0;\n\t"                                                                      \
+        EPSMUL("p0", "p1", "p2") /* + p2*EPS        [2^64 = EPS] */                                    \
+        "addc.u32 m, 0, 0;\n\t" /* + carry*EPS = - carry + (carry << 32) */                            \
+        "sub.cc.u32 p0, p0, m;\n\t"                                                                    \
+        "subc.u32 p1, p1, 0;\n\t"                                                                      \
+        "add.u32 p1, p1, m;\n\t"                                                                       \
+        "mov.b64 %0, {p0,p1};\n\t"                                                                     \
+        "}" : "=l"(r) : "l"(lo), "l"(hi))
+    if (EPSALU) GL_REDUCE128_PTX(GL_PTX_ADD_EPS_MUL_ALU);
+    else GL_REDUCE128_PTX(GL_PTX_ADD_EPS_MUL_FMA);
+#undef GL_REDUCE128_PTX
     return r;
 #else
     uint32_t h0 = (uint32_t)hi, h1 = (uint32_t)(hi >> 32);
@@ -157,6 +178,7 @@ GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi)
     return r;
 #endif
 }
+GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi) { return gl_reduce128_t<GL_EPS_ALU != 0>(lo, hi); }
 
 // full 64x64 -> 128 product as 32-bit limbs (4 IMAD.WIDE.U32)
 GL_HD void gl_mul_wide(gl_t a, gl_t b, gl_t &lo, gl_t &hi)
@@ -195,15 +217,58 @@ GL_HD gl_t gl_mul(gl_t a, gl_t b)
     gl_mul_wide(a, b, lo, hi);
     return gl_reduce128(lo, hi);
 }
+// the same with the reduction's p2*EPS on the fma pipe (for ALU-bound kernels: the NTT passes)
+GL_HD gl_t gl_mul_fma(gl_t a, gl_t b)
+{
+    gl_t lo, hi;
+    gl_mul_wide(a, b, lo, hi);
+    return gl_reduce128_t<false>(lo, hi);
+}
 
-GL_HD gl_t gl_sqr(gl_t a) { return gl_mul(a, a); }
+// a*a: three IMAD.WIDE instead of four (the cross product a0*a1 is computed once and doubled with shifts on the
+// ALU pipe, which has slack in the Poseidon kernels; IMAD.WIDE costs 4 fmaheavy cycles, a shift 2 ALU cycles)
+#ifndef GL_SQR3
+#define GL_SQR3 1
+#endif
+GL_HD void gl_sqr_wide(gl_t a, gl_t &lo, gl_t &hi)
+{
+#if GL_DEVICE_PTX && GL_SQR3
+    asm("{\n\t"
+        ".reg .u32 a0,a1,x0,x1,d0,d1,d2,y0,y1,z0,z1;\n\t"
+        ".reg .u64 X,Y,Z;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mul.wide.u32 Z, a0, a0;\n\t"
+        "mul.wide.u32 X, a0, a1;\n\t"
+        "mul.wide.u32 Y, a1, a1;\n\t"
+        "mov.b64 {x0,x1}, X;\n\t"
+        "mov.b64 {z0,z1}, Z;\n\t"
+        "mov.b64 {y0,y1}, Y;\n\t"
+        "shl.b32 d0, x0, 1;\n\t"                      // 2X = d2:d1:d0 (65 bits)
+        "shf.l.wrap.b32 d1, x0, x1, 1;\n\t"
+        "shr.u32 d2, x1, 31;\n\t"
+        "add.cc.u32 z1, z1, d0;\n\t"
+        "addc.cc.u32 y0, y0, d1;\n\t"
+        "addc.u32 y1, y1, d2;\n\t"
+        "mov.b64 %0, {z0,z1};\n\t"
+        "mov.b64 %1, {y0,y1};\n\t"
+        "}" : "=l"(lo), "=l"(hi) : "l"(a));
+#else
+    gl_mul_wide(a, a, lo, hi);
+#endif
+}
+GL_HD gl_t gl_sqr(gl_t a)
+{
+    gl_t lo, hi;
+    gl_sqr_wide(a, lo, hi);
+    return gl_reduce128(lo, hi);
+}
 
 // x^7, the Poseidon S-box (poseidon_goldilocks.hpp:91-97): 4 multiplies
 GL_HD gl_t gl_pow7(gl_t x)
 {
-    gl_t x2 = gl_mul(x, x);
+    gl_t x2 = gl_sqr(x);
     gl_t x3 = gl_mul(x, x2);
-    gl_t x4 = gl_mul(x2, x2);
+    gl_t x4 = gl_sqr(x2);
     return gl_mul(x3, x4);
 }
 

@@ -118,7 +118,7 @@ static __device__ __forceinline__ gl_t ntt_tw2(const gl_t *lo, const gl_t *hi, u
 {
     const gl_t l = __ldg(lo + (e & ((1u << NTT_LOGT) - 1)));
     const uint64_t h = e >> NTT_LOGT;
-    return h ? gl_mul(l, __ldg(hi + h)) : l;
+    return h ? gl_mul_fma(l, __ldg(hi + h)) : l;
 }
 
 // ---- slow paths, kept out of line so that the unrolled fast path stays small (the kernel must fit the
@@ -157,7 +157,7 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
             const uint32_t t = t0 + (uint32_t)w * tstride;
             const gl_t f = fptr ? __ldg(fptr + ((uint64_t)t << fsh)) : ntt_factor_slow(sl, fkind, p, fbase + ((uint64_t)t << fbsh));
             gl_t &x = v[ntt_slot<LOGX, INV>(w)];
-            x = gl_mul(x, f);
+            x = gl_mul_fma(x, f);
         }
     }
     if (a.canon_out) {
@@ -244,7 +244,7 @@ k_ntt_pass(NttPass a)
             for (int m = 0; m < (QA >> LSH); m++) {
                 const uint32_t q = (uint32_t)m * QB + b;
                 const gl_t f = twp ? __ldg(twp + q) : ntt_factor_slow(sl, INV ? NTT_F_TW_INV : NTT_F_TW, p, q);
-                v[m] = gl_mul(v[m], f);
+                v[m] = gl_mul_fma(v[m], f);
             }
         }
         ntt_dft_regs<A, LSH>(v);
@@ -258,7 +258,7 @@ k_ntt_pass(NttPass a)
             for (int u = 1; u < QA; u++) {
                 uint32_t zi = (b * (uint32_t)u) << (8 - LOGQ);
                 if (INV) zi = (256 - zi) & 255;
-                trow[(size_t)u * QB * NTT_LANES] = gl_mul(v[ntt_slot<A, INV>(u)], __ldg(a.zeta + zi));
+                trow[(size_t)u * QB * NTT_LANES] = gl_mul_fma(v[ntt_slot<A, INV>(u)], __ldg(a.zeta + zi));
             }
         }
     }
@@ -293,7 +293,7 @@ __global__ void k_ntt_pow_table(gl_t *out, gl_t c, gl_t g, uint64_t mul, uint64_
 {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = gl_canon(gl_mul(c, gl_pow(g, i * mul)));
+    out[i] = gl_canon(gl_mul_fma(c, gl_pow(g, i * mul)));
 }
 // pass table: out[p*Q + i] = g^(p*i), p < S, i < Q   (g = w_L or its inverse)
 __global__ void k_ntt_pass_table(gl_t *out, gl_t g, uint32_t logQ, uint64_t n)
@@ -318,5 +318,5 @@ __global__ void k_ntt_scale_table(gl_t *out, gl_t c, gl_t g, NttPlanLogs pl, uin
         j |= (rem & ((1ull << pl.lg[i]) - 1)) << sh;
         rem >>= pl.lg[i];
     }
-    out[pos] = gl_canon(gl_mul(c, gl_pow(g, j)));
+    out[pos] = gl_canon(gl_mul_fma(c, gl_pow(g, j)));
 }

@@ -14,6 +14,7 @@
 //  * Dot products (P layer, partial rounds) accumulate the four partial-product columns unreduced in
 //    64-bit + carry-count accumulators and fold once per 12 terms instead of once per term.
 #pragma once
+#include <math.h>
 #include "gl_field.cuh"
 #include "poseidon_tables.cuh"
 
@@ -27,6 +28,9 @@ GLP_CONSTANT gl_t POS_PRE[144] = {GLP_POSEIDON_PRE_INIT};
 GLP_CONSTANT gl_t POS_SP[GLP_POSEIDON_SP_N] = {GLP_POSEIDON_SP_INIT};
 GLP_CONSTANT gl_t POS_RCF[96] = {GLP_POSEIDON_RCF_INIT};     // full-round constants, one row of 12 per round
 GLP_CONSTANT gl_t POS_PRET[144] = {GLP_POSEIDON_PRET_INIT};  // pre-matrix, transposed: row i = weights of output i
+GLP_CONSTANT gl_t POS_MRC[96] = {GLP_POSEIDON_MRC_INIT};     // round constants pushed through the following linear layer
+GLP_CONSTANT uint32_t POS_MRCL[288] = {GLP_POSEIDON_MRCL_INIT};  // the same, as limbs of 22/22/20 bits
+GLP_CONSTANT double POS_MRCD[192] = {GLP_POSEIDON_MRCD_INIT};    // the same, as 2^52 + 32-bit half (low, high)
 
 #define POS_WIDTH 12
 #define POS_RATE 8
@@ -77,6 +81,12 @@ GL_HD void gl_dot_mac(GlDotAcc &s, gl_t a, gl_t b)
 #endif
 }
 
+#ifndef POS_EPS_ALU_FOLD
+#define POS_EPS_ALU_FOLD 0        // 1: the p2*EPS term of the dot-product folds on the ALU pipe (experiment)
+#endif
+#ifndef POS_EPS_ALU_MULADD
+#define POS_EPS_ALU_MULADD 0      // 1: same for the rank-1 update multiplies of the partial rounds (experiment)
+#endif
 // value = Z + X*2^32 + Y*2^64  ->  limbs l0..l4 (weights 2^0..2^128), then
 //   (l1:l0) + l2*EPS - l3 - l4*2^32   (2^64 = EPS, 2^96 = -1, 2^128 = -2^32)
 GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
@@ -87,7 +97,7 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
     uint64_t l4 = (uint64_t)s.yc + (t3 >> 32);
     gl_t lo = ((t1 & 0xFFFFFFFFULL) << 32) | s.z0;
     gl_t hi = ((t3 & 0xFFFFFFFFULL) << 32) | (t2 & 0xFFFFFFFFULL);
-    gl_t r = gl_reduce128(lo, hi);
+    gl_t r = gl_reduce128_t<POS_EPS_ALU_FOLD != 0>(lo, hi);
     return gl_sub(r, l4 << 32);
 }
 
@@ -103,7 +113,7 @@ GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c)
     hi += (t < lo);
     lo = t;
 #endif
-    return gl_reduce128(lo, hi);
+    return gl_reduce128_t<POS_EPS_ALU_MULADD != 0>(lo, hi);
 }
 
 // ---- MDS layer: state' = M^T state,  M[j][i] = circ[(j-i) mod 12] (+8 at i=j=0) ----
@@ -119,8 +129,7 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
         "mov.b64 {h0,h1}, %2;\n\t"
         "add.cc.u32 l1, l1, h0;\n\t"
         "addc.u32 h1, h1, 0;\n\t"
-        "mad.lo.cc.u32 l0, h1, 0xffffffff, l0;\n\t"
-        "madc.hi.cc.u32 l1, h1, 0xffffffff, l1;\n\t"
+        GL_PTX_ADD_EPS_MUL_ALU("l0", "l1", "h1")
         "addc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 l0, l0, m;\n\t"
         "subc.u32 l1, l1, 0;\n\t"
@@ -168,6 +177,106 @@ GL_HD void pos_mds(gl_t x[12])
     }
 }
 
+// ---- MDS layer in limb form, round constants folded in: x <- M^T x + M^T rc ----
+// IMAD.WIDE occupies the fmaheavy pipe for 4 cycles per warp instruction, a 32-bit IMAD or an ALU op (LEA, shift-add)
+// for 2 (profiles/r01_int_pipes.txt), and the IMAD.WIDE form of this layer (pos_mds) made the kernel fmaheavy-bound
+// with the ALU pipe half idle.  Here every state word is cut into limbs of 22, 22 and 20 bits; limb * coefficient
+// summed over the 12 inputs stays below 2^31 (sum of a row's coefficients is 280), so each output is three chains of
+// 32-bit multiply-adds -- which ptxas is free to issue as IMAD (fma pipe) or, for coefficients like 16, 2, 17, as
+// LEA / shift-add (ALU pipe) -- started from the limbs of the folded round constant, then one recombination and fold.
+#ifndef POS_MDS_LIMB
+#define POS_MDS_LIMB 2          // 0: IMAD.WIDE chains (pos_mds); 1: 22-bit limbs, 32-bit IMAD (pos_mds_limb); 2: FP64 pipe (pos_mds_f64)
+#endif
+GL_HD gl_t pos_mds_combine(uint32_t a0, uint32_t a1, uint32_t a2)
+{
+    // a0 + a1*2^22 + a2*2^44 (< 2^74)  =  lo64 + top*2^64,  then  lo64 + top*EPS  (top < 2^10)
+    uint64_t lo = (uint64_t)a0 + ((uint64_t)a1 << 22);                 // < 2^54
+    const uint64_t hi = (uint64_t)(a2 & 0xFFFFFu) << 44;
+    uint32_t top = a2 >> 20;
+    lo += hi;
+    top += (lo < hi);
+    const uint64_t t = ((uint64_t)top << 32) - top;                     // top * EPS < 2^42
+    uint64_t r = lo + t;
+    if (r < t) r += GL_EPS;                                             // wrapped: r < 2^42, cannot wrap again
+    return r;
+}
+GL_HD void pos_mds_limb(gl_t x[12], const uint32_t *rcl)
+{
+    const uint32_t circ[12] = {GLP_MDS_CIRC_INIT};
+    uint32_t l0[12], l1[12], l2[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) {
+        const uint32_t lo = (uint32_t)x[j], hi = (uint32_t)(x[j] >> 32);
+        l0[j] = lo & 0x3FFFFFu;
+        l1[j] = ((lo >> 22) | (hi << 10)) & 0x3FFFFFu;
+        l2[j] = hi >> 12;
+    }
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        uint32_t a0 = rcl[3 * i], a1 = rcl[3 * i + 1], a2 = rcl[3 * i + 2];
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            const uint32_t c = circ[(j - i + 12) % 12] + ((i == 0 && j == 0) ? GLP_MDS_DIAG0 : 0);
+            a0 += l0[j] * c;
+            a1 += l1[j] * c;
+            a2 += l2[j] * c;
+        }
+        x[i] = pos_mds_combine(a0, a1, a2);
+    }
+}
+
+// ---- MDS layer on the FP64 pipe, round constants folded in: x <- M^T x + M^T rc ----
+// The B200 issues DFMA at 64 lanes/clk/SM -- twice the rate of IMAD.WIDE (profiles/r01_int_pipes.txt: DFMA 63, IMAD.WIDE
+// 32 lanes/clk/SM) -- and a double holds integers below 2^53 exactly.  The IMAD.WIDE form of this layer (pos_mds) needs
+// exactly that range: sum_j c_ij * (32-bit half of x_j) < 2^41.  So each 32-bit half is made a double once (the
+// 0x43300000 exponent trick + one DADD, no I2F), every output half is a 12-term DFMA chain started from
+// 2^52 + (half of the folded round constant), and the integer sum is read back from the mantissa: same arithmetic,
+// half the pipe time, and the ALU pipe only sees the fold.  Every intermediate is an integer < 2^53, so the result is
+// exact whatever the rounding mode; the host emulator runs the same expressions in IEEE double.
+GL_HD double pos_u32_to_f64(uint32_t v)
+{
+#if GL_DEVICE_PTX
+    return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;        // (2^52 + v) - 2^52
+#else
+    return (double)v;
+#endif
+}
+GL_HD uint64_t pos_f64_mantissa(double d)                                        // d = 2^52 + k, k < 2^52  ->  k
+{
+#if GL_DEVICE_PTX
+    return (uint64_t)__double_as_longlong(d) & 0x000FFFFFFFFFFFFFULL;
+#else
+    return (uint64_t)(d - 4503599627370496.0);
+#endif
+}
+GL_HD void pos_mds_f64(gl_t x[12], const double *rcd)
+{
+    const uint32_t circ[12] = {GLP_MDS_CIRC_INIT};
+    uint64_t L[12];
+    {
+        double d[12];
+#pragma unroll
+        for (int j = 0; j < 12; j++) d[j] = pos_u32_to_f64((uint32_t)x[j]);
+#pragma unroll
+        for (int i = 0; i < 12; i++) {
+            double acc = rcd[2 * i];
+#pragma unroll
+            for (int j = 0; j < 12; j++) acc = fma(d[j], (double)(circ[(j - i + 12) % 12] + ((i == 0 && j == 0) ? GLP_MDS_DIAG0 : 0)), acc);
+            L[i] = pos_f64_mantissa(acc);
+        }
+    }
+    double d[12];
+#pragma unroll
+    for (int j = 0; j < 12; j++) d[j] = pos_u32_to_f64((uint32_t)(x[j] >> 32));
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+        double acc = rcd[2 * i + 1];
+#pragma unroll
+        for (int j = 0; j < 12; j++) acc = fma(d[j], (double)(circ[(j - i + 12) % 12] + ((i == 0 && j == 0) ? GLP_MDS_DIAG0 : 0)), acc);
+        x[i] = pos_mds_fold(L[i], pos_f64_mantissa(acc));
+    }
+}
+
 // ---- the permutation ----
 // Code layout matters as much as the arithmetic here: a fully unrolled permutation is ~125 KB of SASS, four
 // times the instruction cache, and with 16 warps of an SM at 16 different places in it the kernel stalls on
@@ -179,7 +288,8 @@ GL_HD void pos_mds(gl_t x[12])
 #define POS_SBOX_GROUP 12         // S-boxes per trip of the S-box loop (12 = unrolled; 4 or 6 = rolled with a rotating state: smaller code, measured 2-5 % slower)
 #endif
 #ifndef POS_ROLL_PRE
-#define POS_ROLL_PRE 0            // 1 = 12-trip pre-matrix loop with a register queue (3 KB instead of 30 KB of code, measured 1-2 % slower)
+#define POS_ROLL_PRE 1            // 1 = 12-trip pre-matrix loop with a register queue: 3 KB instead of 30 KB of code.  With the FP64 MDS layer the
+                                  // unrolled form pushes the kernel past the 32 KB L1.5 instruction cache and costs 4.5 % (profiles/r01_poseidon_variants.txt)
 #endif
 
 template <bool LOCKSTEP>
@@ -191,10 +301,16 @@ GL_HD void pos_round_sync()
 }
 
 // x_i = x_i^7 + rc_i for all 12, as 12/G trips over G lanes with the state rotated by G after each trip
+// (rc == NULL: no constant here, it was folded into the linear layer that follows -- POS_MDS_LIMB)
 GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc)
 {
     constexpr int G = POS_SBOX_GROUP;
     static_assert(12 % G == 0, "POS_SBOX_GROUP must divide 12");
+    if (!rc) {
+#pragma unroll
+        for (int i = 0; i < 12; i++) x[i] = gl_pow7(x[i]);
+        return;
+    }
     if (G == 12) {
 #pragma unroll
         for (int i = 0; i < 12; i++) x[i] = gl_add_c(gl_pow7(x[i]), rc[i]);
@@ -224,6 +340,10 @@ GL_HD void pos_pre_layer(gl_t x[12])
         const gl_t *col = POS_PRET + 12 * i;
         GlDotAcc acc;
         gl_dot_init(acc);
+#if POS_MDS_LIMB
+        acc.z0 = (uint32_t)POS_MRC[36 + i];
+        acc.z1 = (uint32_t)(POS_MRC[36 + i] >> 32);
+#endif
 #pragma unroll
         for (int j = 0; j < 12; j++) gl_dot_mac(acc, x[j], col[j]);
 #pragma unroll
@@ -240,6 +360,10 @@ GL_HD void pos_pre_layer(gl_t x[12])
     for (int i = 0; i < 12; i++) {
         GlDotAcc acc;
         gl_dot_init(acc);
+#if POS_MDS_LIMB
+        acc.z0 = (uint32_t)POS_MRC[36 + i];              // + PRE^T rc_3 (see POS_MRC)
+        acc.z1 = (uint32_t)(POS_MRC[36 + i] >> 32);
+#endif
 #pragma unroll
         for (int j = 0; j < 12; j++) gl_dot_mac(acc, y[j], POS_PRE[j * 12 + i]);
         x[i] = gl_dot_fold(acc);
@@ -258,10 +382,21 @@ GL_HD void pos_permute_t(gl_t x[12])
 #pragma unroll 1
     for (int r = 0; r < 8; r++) {
         pos_round_sync<LOCKSTEP>();
+#if POS_MDS_LIMB
+        pos_sbox_layer(x, nullptr);                      // constants ride in the linear layer's accumulators
+        if (r != 3) {
+#if POS_MDS_LIMB == 2
+            pos_mds_f64(x, POS_MRCD + 24 * r);
+#else
+            pos_mds_limb(x, POS_MRCL + 36 * r);
+#endif
+        } else {
+#else
         pos_sbox_layer(x, POS_RCF + 12 * r);
         if (r != 3) {
             pos_mds(x);
         } else {
+#endif
             pos_pre_layer(x);
             // partial rounds: x0 = x0^7 + C;  s0 = <x, S[0..12)>;  x_i += x0 * S[11+i] (i >= 1);  x0 = s0
 #pragma unroll 1

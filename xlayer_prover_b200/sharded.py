@@ -28,11 +28,12 @@ def column_bounds(ncols, world):
     return [min(ncols, 8 * ((g * nblk) // world)) for g in range(world)] + [ncols]
 
 
-def assemble_tree(subtrees, n_ext, world):
+def assemble_tree(subtrees, n_ext, world, empty=None):
     """Re-lay G row-sharded subtrees (each (2R-1)*4 words, level-major) into the first
     levels of the full level-major tree; returns (full_tree, offset_of_level_with_G_nodes)."""
     R = n_ext // world
-    full = torch.zeros(tree_num_elements(n_ext), dtype=torch.int64, device=subtrees[0].device)
+    full = (empty(tree_num_elements(n_ext)) if empty is not None else
+            torch.empty(tree_num_elements(n_ext), dtype=torch.int64, device=subtrees[0].device))
     off_full, off_sub, n_full, n_sub = 0, 0, n_ext, R
     while n_sub >= 1:
         for g, t in enumerate(subtrees):
@@ -50,7 +51,7 @@ class ShardedCommit:
     """commit(in_slice) for one rank.  `ctx` is this rank's glprover Context; `device` the torch device the
     buffers live on ('cuda:N', or 'cpu' with the emulator backend in the gloo tests)."""
 
-    def __init__(self, ctx, n, n_ext, ncols, group=None, device=None):
+    def __init__(self, ctx, n, n_ext, ncols, group=None, device=None, alloc=None):
         self.ctx, self.n, self.n_ext, self.ncols = ctx, n, n_ext, ncols
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -62,13 +63,16 @@ class ShardedCommit:
         self.w = self.c1 - self.c0
         self.R = n_ext // self.world
         i64 = dict(dtype=torch.int64, device=self.device)
+        # alloc(nwords) -> int64 tensor; the gloo tests pass one that carves "device" memory out of the emulator
+        empty = alloc if alloc is not None else (lambda nwords: torch.empty(nwords, **i64))
         # buffer A holds my columns for all rows (LDE output), then -- after the exchange -- my rows for all
         # columns (the slab the Merkle stage reads); buffer B receives the all-to-all.  Peak = A + B.
-        self.buf_a = torch.empty(max(1, n_ext * self.w, self.R * ncols), **i64)
+        self.buf_a = empty(max(1, n_ext * self.w, self.R * ncols))
         self.ext_cols = self.buf_a[: max(1, n_ext * self.w)]
         self.slab = self.buf_a[: self.R * ncols]
-        self.recv = torch.empty(self.R * ncols, **i64) if self.world > 1 else None
-        self.subtree = torch.empty(tree_num_elements(self.R), **i64)
+        self.recv = empty(self.R * ncols) if self.world > 1 else None
+        self.subtree = empty(tree_num_elements(self.R))
+        self._empty = empty
         self.tree = None
 
     def bind_stream(self):
@@ -111,7 +115,7 @@ class ShardedCommit:
         dist.gather(self.subtree, gathered, dst=0, group=self.group)
         if self.rank != 0:
             return None
-        self.tree, off_top = assemble_tree(gathered, self.n_ext, G)
+        self.tree, off_top = assemble_tree(gathered, self.n_ext, G, self._empty)
         self.ctx.merkle_levels(self.tree[off_top:], G)
         return self.tree[-4:].clone()
 
