@@ -37,7 +37,12 @@ if ROOT not in sys.path:
 
 P = 0xFFFFFFFF00000001
 SEED = 0x9E3779B97F4A7C15 + 2          # seed = golden ratio + config id
-SASS_INSTR_PER_PERM = 24143            # tools/sass_count.py on k_permute_batch (profiles/r01_sass_counts.txt)
+# Pipe cycles one warp needs for one permutation inside k_linear_hash_rows, from its SASS (tools/sass_mix.py with the loop
+# trip counts 8/7/12/22) and the pipe costs measured on this GPU (profiles/r01_int_pipes.txt: IMAD.WIDE and IMAD.HI 4 cycles
+# per warp instruction per SM sub-partition, other IMAD, DFMA/DADD and every ALU op 2, one issue per cycle).  DFMA shares its
+# dispatch with IMAD.WIDE (DFMA+IMAD.WIDE pairs take 5.5 cycles, 6 if serial), so the multiplier bound counts both.
+POS_PIPE_CYCLES = {"fmaheavy": 25426, "fp64": 4368, "alu": 21712, "issue": 21905}
+POS_BOUND_CYCLES = POS_PIPE_CYCLES["fmaheavy"] + POS_PIPE_CYCLES["fp64"]
 
 
 def parse_args():
@@ -379,13 +384,15 @@ def main_ours(args):
                          "frac": (leaf_gbs / hbm_peak) if leaf_gbs else None, "traffic": None, "peak_source": peak_src,
                          "launch_ms": leaf_ms, "algorithmic_bytes_per_launch": leaf_bytes,
                          "note": "dominant kernel by time; it is integer-issue bound, not HBM bound -- see roofline_int"},
-            "roofline_int": {"kernel": "k_linear_hash_rows", "bound": "integer issue (IMAD + IADD3 pipes)",
-                             "achieved": leaf_perms * SASS_INSTR_PER_PERM / (leaf_ms * 1e-3) if leaf_ms > 0 else None,
-                             "peak": int_peak["interleaved_lane_ops_per_s"], "unit": "lane-instr/s",
-                             "frac": (leaf_perms * SASS_INSTR_PER_PERM / (leaf_ms * 1e-3) / int_peak["interleaved_lane_ops_per_s"]) if leaf_ms > 0 else None,
-                             "instr_per_permutation": SASS_INSTR_PER_PERM, "measured_peaks": int_peak,
-                             "leaf_hash_perm_per_s": leaf_perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None},
-            "roofline_lde": {"kernels": "k_ntt_tile x4 passes per column block", "bound": "hbm", "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms > 0 else None,
+            "roofline_int": {"kernel": "k_linear_hash_rows", "bound": "integer multiplier pipes (fmaheavy IMAD.WIDE + FP64 DFMA)",
+                             "achieved": leaf_perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None,
+                             "peak": 148 * 4 * 32 * (result["clocks"].get("sm_mhz") or 1965.0) * 1e6 / POS_BOUND_CYCLES,
+                             "unit": "Poseidon permutations/s",
+                             "frac": (leaf_perms / (leaf_ms * 1e-3)) / (148 * 4 * 32 * (result["clocks"].get("sm_mhz") or 1965.0) * 1e6 / POS_BOUND_CYCLES) if leaf_ms > 0 else None,
+                             "pipe_cycles_per_warp_permutation": POS_PIPE_CYCLES, "measured_lane_ops_per_s": int_peak,
+                             "note": "peak = 148 SMs x 4 sub-partitions x 32 lanes x SM clock / multiplier-pipe cycles per warp-permutation; "
+                                     "ncu (profiles/r01_ncu_full_summary_call7.txt): fmaheavy 68 % busy, ALU 59 %, FP64 12 %, issue 60 %"},
+            "roofline_lde": {"kernels": "k_ntt_pass: 3 INTT + 3 NTT tile passes per column block", "bound": "hbm", "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms > 0 else None,
                              "peak": hbm_peak, "unit": "GB/s", "frac": (lde_bytes / (lde_ms * 1e-3) / 1e9 / hbm_peak) if lde_ms > 0 else None,
                              "algorithmic_bytes": lde_bytes, "design_traffic_bytes": 8.0 * wcols * (5 * n + 3 * n_ext), "lde_ms": lde_ms},
             "clocks": result["clocks"], "gpu_launches": result["launches"], "e2e": result["e2e"],
@@ -447,17 +454,8 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
         def step():
             return ctx.commit(hext_p, htree_p, hin_p, n, n_ext, C)
     else:
-        din = torch.empty(max(1, n * w), dtype=torch.int64, device=dev)
-
         def step():
-            din.copy_(hin, non_blocking=True)
-            root = sc.commit(din)
-            if hext is not None:
-                hext.copy_(sc.slab, non_blocking=True)
-            if rank == 0:
-                htree.copy_(sc.tree, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
-            return root
+            return sc.commit_host(hin_p, hext, htree if rank == 0 else None)
     for _ in range(min(W, 3)):
         step()
     barrier()

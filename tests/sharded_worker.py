@@ -34,6 +34,14 @@ def main():
     din[: n * sc.w] = torch.from_numpy(a.view(np.int64).reshape(-1).copy())
     root = sc.commit(din)
     slab = to_numpy_u64(sc.slab).reshape(sc.R, ncols).copy()
+    tree = to_numpy_u64(sc.tree).copy() if rank == 0 else None
+    # the host-pointer flavour (what bench.py's e2e leg runs at N > 1) must give the same slab, tree and root
+    hext = torch.zeros(sc.R * ncols, dtype=torch.int64)
+    htree = torch.zeros(sc.subtree.numel() * 0 + (2 * n_ext - 1) * 4, dtype=torch.int64) if rank == 0 else None
+    root2 = sc.commit_host(np.ascontiguousarray(a), hext, htree)
+    assert np.array_equal(to_numpy_u64(hext).reshape(sc.R, ncols), slab), "commit_host slab differs"
+    if rank == 0:
+        assert np.array_equal(to_numpy_u64(root2), to_numpy_u64(root)) and np.array_equal(to_numpy_u64(htree), tree), "commit_host tree differs"
     slabs = [None] * world
     dist.gather_object(slab, slabs if rank == 0 else None, dst=0)
     if rank == 0:

@@ -74,6 +74,31 @@ int main()
         }
         cudaFree(d3);
     }
+    // one block's download split over k streams (row ranges), alone and under a concurrent 2-D upload
+    {
+        cudaStream_t ss[4];
+        for (int i = 0; i < 4; i++) CK(cudaStreamCreateWithFlags(&ss[i], cudaStreamNonBlocking));
+        cudaStream_t sup;
+        CK(cudaStreamCreateWithFlags(&sup, cudaStreamNonBlocking));
+        const size_t wb = 96;
+        for (int withup = 0; withup < 2; withup++)
+            for (int k : {1, 2, 4}) {
+                CK(cudaDeviceSynchronize());
+                CK(cudaEventRecord(a, ss[0]));
+                for (int i = 1; i < k; i++) CK(cudaStreamWaitEvent(ss[i], a, 0));
+                if (withup) { CK(cudaStreamWaitEvent(sup, a, 0)); CK(cudaMemcpy2DAsync(d2, wb * 8, h + 400, C * 8, wb * 8, rows, cudaMemcpyHostToDevice, sup)); }
+                for (int i = 0; i < k; i++) {
+                    const size_t r0 = rows / k * i, nr = rows / k;
+                    CK(cudaMemcpy2DAsync(h + 8 + r0 * C, C * 8, d + 8 + r0 * C, C * 8, wb * 8, nr, cudaMemcpyDeviceToHost, ss[i]));
+                }
+                for (int i = 1; i < k; i++) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); CK(cudaEventRecord(e, ss[i])); CK(cudaStreamWaitEvent(ss[0], e, 0)); }
+                CK(cudaEventRecord(b, ss[0])); CK(cudaEventSynchronize(b)); CK(cudaEventElapsedTime(&ms, a, b));
+                char nm[128];
+                snprintf(nm, sizeof nm, "D2H 2-D 96 cols over %d stream(s)%s (D2H bytes only)", k, withup ? " + concurrent 2-D upload" : "");
+                rep(nm, (double)rows * wb * 8);
+                CK(cudaDeviceSynchronize());
+            }
+    }
     // pageable
     uint64_t *pg = (uint64_t *)malloc(big);
     for (size_t i = 0; i < big / 8; i += 512) pg[i] = i;

@@ -127,5 +127,37 @@ class ShardedCommit:
         return self.finish()
 
 
+    def commit_host(self, host_in, host_ext=None, host_tree=None):
+        """The same commit with this rank's column slice in (pinned) HOST memory and the results wanted on the host:
+        host_in = address or array of the [n x w] slice, host_ext = pinned tensor for this rank's [R x C] row slab,
+        host_tree = pinned tensor for the whole tree (rank 0).  Uploads overlap the LDE column block by column block
+        (glp_extend_pol's streamed path); the slab's download runs on a side stream while the leaves are hashed."""
+        self.bind_stream()
+        if self.w:
+            self.ctx.extend_pol(self.ext_cols, host_in, self.n_ext, self.n, self.w)
+        self.exchange()
+        cuda = self.device.type == "cuda"
+        if host_ext is not None:
+            if cuda:
+                if not hasattr(self, "_side"):
+                    self._side = torch.cuda.Stream(device=self.device)
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.device))
+                self._side.wait_event(ev)
+                with torch.cuda.stream(self._side):
+                    host_ext.copy_(self.slab, non_blocking=True)
+            else:
+                host_ext.copy_(self.slab)
+        self.merkle()
+        root = self.finish()
+        if host_tree is not None and self.rank == 0:
+            host_tree.copy_(self.tree, non_blocking=True)
+        if cuda:
+            torch.cuda.current_stream(self.device).synchronize()
+            if host_ext is not None:
+                self._side.synchronize()
+        return root
+
+
 def to_numpy_u64(t):
     return t.detach().cpu().numpy().view(np.uint64)
