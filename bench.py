@@ -206,7 +206,7 @@ def main_reference(args):
         "e2e": {"value": base["value"], "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "poseidon_hash_per_s": base["poseidon_hash_per_s"], "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -375,7 +375,7 @@ def main_ours(args):
             "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
                                    % (args.log_rows, C, args.log_rows + args.log_blowup),
                        "l2_policy": "inputs (%.1f GB) far larger than the 126 MB L2; no flush needed" % (8.0 * n * C / 1e9),
-                       "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d -> NCCL all-to-all -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
+                       "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d whose last NTT pass stores into the peers' row slabs over NVLink (fused exchange) -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
                        "seed": hex(SEED)},
             "commit_ms": result["ms_per_step"], "poseidon_hash_per_s": perms / sec,
             "stage_ms": {"intt": prof["intt"][0] / K, "ntt_ext": prof["ntt_ext"][0] / K, "leaf_hash": prof["leaf_hash"][0] / K,
@@ -404,7 +404,9 @@ def main_ours(args):
                 line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
             except Exception as ex:
                 line["cpu_baseline"] = {"error": repr(ex)}
-        print(json.dumps(line))
+        emit(line)
+    if sc is not None:
+        sc.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -478,8 +480,30 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
                     ([int(x) for x in root.cpu().numpy().view(np.uint64)] if root is not None else None)}
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries write banners to stdout (NCCL prints its version there); the contract is ONE JSON line on stdout.
+    Everything else goes to stderr until emit() restores the descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+    if _REAL_STDOUT is not None:
+        os.dup2(2, 1)                              # anything printed during teardown goes to stderr again
+
+
 def main():
     args = parse_args()
+    quiet_stdout()
     if args.impl == "reference":
         return main_reference(args)
     return main_ours(args)

@@ -71,6 +71,20 @@ int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n_e
  * of the multi-GPU path (each rank extends its own column slice; north_star / SURVEY 8e). */
 int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_pitch, const uint64_t *in, uint64_t in_pitch,
                            uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* The same extension with its OUTPUT row-sharded: row i of the result (i < n_ext) is written to
+ * parts[i / R] + (i % R) * part_pitch + part_col0, R = n_ext / nparts (nparts a power of two).  This is the multi-GPU
+ * exchange of SURVEY 8e fused into the transform: rank g passes the row slabs of all ranks (its own, and its peers'
+ * mapped with glp_ipc_import), part_col0 = its first column, and the last NTT pass stores every tile straight into the
+ * owner's reference-layout [R x part_pitch] slab over NVLink -- no all-to-all, no re-interleave pass.  Asynchronous on
+ * the context's stream when `in` is a device pointer; a host `in` is uploaded column block by column block under the
+ * transform of the previous block and the call returns when everything has been stored.  `parts` is a host array. */
+int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint32_t nparts, uint64_t part_pitch, uint64_t part_col0,
+                           const uint64_t *in, uint64_t in_pitch, uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* CUDA IPC plumbing for the above (one process per GPU): export a glp_device_alloc'ed buffer as 64 opaque bytes,
+ * map a peer's buffer into this process, unmap it. */
+int glp_ipc_export(glp_ctx *ctx, void *devptr, unsigned char handle[64]);
+int glp_ipc_import(glp_ctx *ctx, const unsigned char handle[64], void **devptr);
+int glp_ipc_close(glp_ctx *ctx, void *devptr);
 /* NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305): dst[i, 0:ncols] = src[BR(i), offset_cols : offset_cols+ncols]
  * (dst rows have ncols words, src rows ncols_all).  With extension > 1 rows whose source index is >= size/extension
  * are zero-filled.  dst == src permutes in place (requires ncols == ncols_all, offset_cols == 0, extension <= 1). */

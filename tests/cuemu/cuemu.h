@@ -98,5 +98,11 @@ cudaError_t cudaSetDevice(int d);
 cudaError_t cudaGetDevice(int *d);
 cudaError_t cudaMemGetInfo(size_t *free_, size_t *total);
 cudaError_t cudaPointerGetAttributes(cudaPointerAttributes *a, const void *p);
+// IPC inside one process: the "handle" is the pointer itself (enough to exercise export/import/scatter on the CPU)
+struct cudaIpcMemHandle_t { char reserved[64]; };
+enum { cudaIpcMemLazyEnablePeerAccess = 1 };
+cudaError_t cudaIpcGetMemHandle(cudaIpcMemHandle_t *h, void *p);
+cudaError_t cudaIpcOpenMemHandle(void **p, cudaIpcMemHandle_t h, unsigned flags);
+cudaError_t cudaIpcCloseMemHandle(void *p);
 cudaError_t cudaGetDeviceProperties(cudaDeviceProp *p, int dev);
 template <class F> static inline cudaError_t cudaFuncSetAttribute(F, cudaFuncAttribute, int) { return cudaSuccess; }

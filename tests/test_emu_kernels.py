@@ -134,6 +134,50 @@ def check_absorb(ctx, oracle, rng):
     ctx.device_free(ds)
 
 
+def check_scatter(ctx, oracle, rng, shapes=((64, 2, 21), (32, 4, 9), (16, 2, 40), (1, 2, 3)), use_ipc=True):
+    """extendPol with a row-sharded output: nparts slabs [R x pitch], this call owning columns col0..col0+ncols"""
+    for n, blow, ncols in shapes:
+        n_ext = n * blow
+        a = edge_matrix(rng, n, ncols)
+        want = oracle.extend_pol(a, n_ext)
+        da = ctx.to_device(a)
+        for nparts in (1, 2, 4):
+            if nparts > n_ext:
+                continue
+            R, pitch, col0 = n_ext // nparts, ncols + 11, 5
+            slabs = [ctx.device_alloc(R * pitch * 8) for _ in range(nparts)]
+            for sl in slabs:
+                ctx.memcpy(sl, np.full(R * pitch, 0x5555, dtype=np.uint64), R * pitch * 8)
+            # slabs reached through an exported + imported handle, as a peer rank would (the emulator allows that inside
+            # one process; CUDA does not, so on the GPU the IPC leg is covered by the multi-rank run of bench.py)
+            mapped = [ctx.ipc_import(ctx.ipc_export(sl)) if (i % 2 and use_ipc) else sl for i, sl in enumerate(slabs)]
+            ctx.extend_pol_scatter(mapped, pitch, col0, da if nparts != 2 else a, ncols, n_ext, n, ncols)   # nparts 2: host input
+            ctx.synchronize()
+            for g, sl in enumerate(slabs):
+                got = ctx.to_host(sl, (R, pitch))
+                check_equal(got[:, col0:col0 + ncols], want[g * R:(g + 1) * R], "scatter %s parts=%d slab %d" % ((n, blow, ncols), nparts, g))
+                assert (got[:, :col0] == 0x5555).all() and (got[:, col0 + ncols:] == 0x5555).all(), "scatter wrote outside its columns"
+                ctx.device_free(sl)
+        ctx.device_free(da)
+
+
+def test_extend_pol_scatter(emu_lib, ectx, ectx3, oracle, rng):
+    check_scatter(ectx, oracle, rng)
+    check_scatter(ectx3, oracle, rng)                        # 2- and 3-pass plans
+    ectx3.set_scratch_limit(1)                               # one column per block
+    try:
+        check_scatter(ectx3, oracle, rng, shapes=((64, 2, 5),))
+    finally:
+        ectx3.set_scratch_limit(0)
+    os.environ["GLP_NTT_NO_FUSED_LDE"] = "1"                 # the copy-kernel fallback
+    try:
+        c = make_ctx(emu_lib)
+    finally:
+        os.environ.pop("GLP_NTT_NO_FUSED_LDE", None)
+    check_scatter(c, oracle, rng, shapes=((32, 2, 7),))
+    c.close()
+
+
 def test_linear_hash_absorb(ectx, oracle, rng):
     check_absorb(ectx, oracle, rng)
 
@@ -166,6 +210,7 @@ def test_commit_streamed_short_first_block(emu_lib, oracle, rng):
         os.environ.pop("GLP_STREAM_COLS", None)
     a = edge_matrix(rng, 16, 100)
     check_commit(c, oracle, a, 32)
+    check_scatter(c, oracle, rng, shapes=((16, 2, 100),))     # host input in 3 upload blocks
     c.close()
 
 

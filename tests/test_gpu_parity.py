@@ -287,6 +287,12 @@ def test_merkletreegl_vs_reference_class(ctx, reference, rng):
         check_equal(mt.getGroupProof(np.zeros(21 + 4 * psize, dtype=np.uint64), idx), gp(idx), "proof %d" % idx)
 
 
+def test_extend_pol_scatter(ctx, oracle, rng):
+    """row-sharded LDE output (the fused multi-GPU exchange) with all slabs on this GPU"""
+    from test_emu_kernels import check_scatter
+    check_scatter(ctx, oracle, rng, shapes=((1 << 10, 2, 37), (1 << 12, 4, 9), (1 << 9, 8, 70), (64, 2, 21), (1, 2, 3)), use_ipc=False)
+
+
 def test_linear_hash_absorb(ctx, oracle, rng):
     from test_emu_kernels import check_absorb
     check_absorb(ctx, oracle, rng)

@@ -36,6 +36,10 @@ SIGNATURES = {
     "glp_ntt": (i32, [vp, vp, vp, u64, u64, i32, i32]),
     "glp_extend_pol": (i32, [vp, vp, vp, u64, u64, u64]),
     "glp_extend_pol_pitched": (i32, [vp, vp, u64, vp, u64, u64, u64, u64]),
+    "glp_extend_pol_scatter": (i32, [vp, C.POINTER(vp), u32, u64, u64, vp, u64, u64, u64, u64]),
+    "glp_ipc_export": (i32, [vp, vp, C.c_char_p]),
+    "glp_ipc_import": (i32, [vp, C.c_char_p, C.POINTER(vp)]),
+    "glp_ipc_close": (i32, [vp, vp]),
     "glp_reverse_permutation": (i32, [vp, vp, vp, u64, u64, u64, u64, u64]),
     "glp_root": (u64, [u32, u64]),
     "glp_hash_full_result": (i32, [vp, vp, vp, u64]),
@@ -178,6 +182,23 @@ class Context:
 
     def extend_pol_pitched(self, out, out_pitch, inp, in_pitch, n_ext, n, ncols):
         self.lib.check(self.lib.glp_extend_pol_pitched(self.h, ptr_of(out), out_pitch, ptr_of(inp), in_pitch, n_ext, n, ncols))
+
+    def extend_pol_scatter(self, parts, part_pitch, part_col0, inp, in_pitch, n_ext, n, ncols):
+        """parts: list of slab base addresses (ints or tensors), one per rank."""
+        arr = (vp * len(parts))(*[ptr_of(x) for x in parts])
+        self.lib.check(self.lib.glp_extend_pol_scatter(self.h, arr, len(parts), part_pitch, part_col0, ptr_of(inp), in_pitch, n_ext, n, ncols))
+
+    def ipc_export(self, devptr):
+        buf = C.create_string_buffer(64)
+        self.lib.check(self.lib.glp_ipc_export(self.h, ptr_of(devptr), buf))
+        return buf.raw
+
+    def ipc_import(self, handle):
+        p = vp()
+        self.lib.check(self.lib.glp_ipc_import(self.h, handle, C.byref(p)))
+        return p.value
+
+    def ipc_close(self, devptr): self.lib.check(self.lib.glp_ipc_close(self.h, devptr))
 
     def reverse_permutation(self, dst, src, size, offset_cols, ncols, ncols_all, extension=1):
         self.lib.check(self.lib.glp_reverse_permutation(self.h, ptr_of(dst), ptr_of(src), size, offset_cols, ncols, ncols_all, extension))

@@ -62,6 +62,7 @@ struct glp_ctx {
     DevBuf s1, s2;                           // NTT scratch
     DevBuf ext, nodes, tmp_in, tmp_out;      // commit / staging
     DevBuf partial;                          // checksum partials
+    DevBuf work, parts_tab;                  // row-sharded LDE: dense block before its last pass, table of slab bases
     std::vector<void *> tables;              // everything to free
     bool profiling = false;
     struct ProfSpan { int kind; cudaEvent_t a, b; };
@@ -163,7 +164,7 @@ extern "C" void glp_destroy(glp_ctx *ctx)
     cudaStreamSynchronize(ctx->stream);
     for (void *p : ctx->tables) cudaFree(p);
     release(ctx->s1); release(ctx->s2); release(ctx->ext); release(ctx->nodes);
-    release(ctx->tmp_in); release(ctx->tmp_out); release(ctx->partial);
+    release(ctx->tmp_in); release(ctx->tmp_out); release(ctx->partial); release(ctx->work); release(ctx->parts_tab);
     cudaStreamDestroy(ctx->own_stream);
     cudaStreamDestroy(ctx->copy_stream[0]);
     cudaStreamDestroy(ctx->copy_stream[1]);
@@ -477,8 +478,15 @@ static int run_transform(glp_ctx *ctx, uint32_t logN, const gl_t *in, uint64_t i
 // digit-reversed out, in place in scratch S = 2^logN x wb), coset scaling on its last pass, then the size-2^(logN+e)
 // forward NTT decimation-in-time with the same radices, reading S and finishing in place in `out`.
 // Returns 1 when the shape has no such plan (caller falls back to two natural-order transforms).
+// where the rows of an extension go when it is row-sharded over several slabs (multi-GPU: one slab per rank)
+struct ScatterDst {
+    const unsigned long long *parts;         // device array of nparts slab bases
+    uint32_t nparts, log_part_rows;
+    uint64_t pitch, col0;
+};
+
 static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t wb,
-                   gl_t *S)
+                   gl_t *S, const ScatterDst *sc = nullptr)
 {
     const uint32_t logM = logN + e;
     NttPlanLogs q, r;
@@ -546,6 +554,13 @@ static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint
             a.tw_mode = first ? NTT_TW_NONE : NTT_TW_PRE;
             a.tw = tab;
             a.canon_out = last;
+            if (last && sc) {                                     // the exchange rides on the last pass's stores
+                a.parts = sc->parts;
+                a.nparts = sc->nparts;
+                a.log_part_rows = sc->log_part_rows;
+                a.part_pitch = sc->pitch;
+                a.part_col0 = sc->col0;
+            }
             uint32_t lsh = 0;
             if (first && e >= 1 && e <= 3) lsh = e;              // used by the kernels whose high digit of q is 4 bits wide
             GLP(launch_pass(ctx, a, q.lg[i], false, lsh));
@@ -594,12 +609,21 @@ static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src,
 }
 
 // one column block of the extension: in (n rows) -> out (n_ext rows); S holds n x w words, S2 n_ext x w (fallback only)
-static int lde_block(glp_ctx *ctx, uint32_t logN, uint32_t logE, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t w)
+static int lde_block(glp_ctx *ctx, uint32_t logN, uint32_t logE, const gl_t *in, uint64_t in_pitch, gl_t *out, uint64_t out_pitch, uint32_t w,
+                     const ScatterDst *sc = nullptr)
 {
     const uint64_t n = 1ull << logN, n_ext = 1ull << logE;
     GLP(ensure(ctx, ctx->s2, (size_t)n * w * sizeof(gl_t)));
-    int rc = ctx->no_fused_lde ? 1 : run_lde(ctx, logN, logE - logN, in, in_pitch, out, out_pitch, w, (gl_t *)ctx->s2.p);
+    int rc = ctx->no_fused_lde ? 1 : run_lde(ctx, logN, logE - logN, in, in_pitch, out, out_pitch, w, (gl_t *)ctx->s2.p, sc);
     if (rc != 1) return rc;
+    if (sc) {                                                     // no fused plan for this shape: extend into `out`, then scatter its rows
+        GLP(lde_block(ctx, logN, logE, in, in_pitch, out, out_pitch, w, nullptr));
+        const uint64_t nb = (n_ext * w + 255) / 256;
+        LAUNCH_FLAT(ctx, k_ntt_scatter_rows, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, sc->parts, sc->log_part_rows, sc->pitch, sc->col0,
+                    (const gl_t *)out, out_pitch, n_ext, (uint64_t)w);
+        CU(cudaGetLastError());
+        return GLP_OK;
+    }
     // fallback: two natural-order transforms (INTT with coset scaling, then the zero-padded forward NTT)
     NttPlanLogs pe;
     if (!plan_passes(ctx, logE, &pe)) return fail(GLP_E_ARG, "NTT: size exceeds four tile passes");
@@ -715,6 +739,99 @@ extern "C" int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_
     CU(cudaSetDevice(ctx->device));
     if (!on_device(in) || !on_device(out)) return fail(GLP_E_ARG, "glp_extend_pol_pitched: device pointers required");
     GLP(dev_extend_pol(ctx, (gl_t *)out, out_pitch, (const gl_t *)in, in_pitch, n_ext, n, ncols));
+    return GLP_OK;
+}
+
+extern "C" int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint32_t nparts, uint64_t part_pitch, uint64_t part_col0,
+                                      const uint64_t *in, uint64_t in_pitch, uint64_t n_ext, uint64_t n, uint64_t ncols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n == 0 || ncols == 0) return GLP_OK;
+    if (!parts || !in) return fail(GLP_E_ARG, "glp_extend_pol_scatter: NULL pointer");
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GLP_E_ARG, "extend_pol: sizes must be powers of two with n_ext >= n");
+    if (n_ext > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    if (!is_pow2(nparts) || nparts > n_ext || nparts > 64) return fail(GLP_E_ARG, "glp_extend_pol_scatter: nparts must be a power of two <= min(n_ext, 64)");
+    if (in_pitch < ncols || part_pitch < part_col0 + ncols) return fail(GLP_E_ARG, "glp_extend_pol_scatter: pitch too small");
+    CU(cudaSetDevice(ctx->device));
+    for (uint32_t i = 0; i < nparts; i++)
+        if (!parts[i]) return fail(GLP_E_ARG, "glp_extend_pol_scatter: NULL slab");
+    GLP(ensure(ctx, ctx->parts_tab, 64 * sizeof(unsigned long long)));
+    CU(cudaMemcpyAsync(ctx->parts_tab.p, parts, nparts * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->stream));
+    const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
+    ScatterDst sc = {(const unsigned long long *)ctx->parts_tab.p, nparts, logE - ilog2_u64(nparts), part_pitch, part_col0};
+    if (!on_device(in)) {
+        // host input: upload column block k+1 (strided 2-D copy) while block k is extended and scattered
+        uint64_t w = ctx->stream_cols;
+        if (w > ncols) w = ncols;
+        const uint64_t nblocks = (ncols + w - 1) / w;
+        GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * w * sizeof(gl_t)));
+        GLP(ensure(ctx, ctx->work, (size_t)n_ext * w * sizeof(gl_t)));
+        gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
+        std::vector<cudaEvent_t> up(nblocks), used(nblocks);
+        for (uint64_t k = 0; k < nblocks; k++) {
+            CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&used[k], cudaEventDisableTiming));
+        }
+        cudaEvent_t start;
+        CU(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+        CU(cudaEventRecord(start, ctx->stream));
+        CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
+        auto width = [&](uint64_t k) { return (uint32_t)((ncols - k * w < w) ? ncols - k * w : w); };
+        auto upload = [&](uint64_t k) -> int {
+            if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], used[k - 2], 0));
+            CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)width(k) * 8, in + k * w, (size_t)in_pitch * 8, (size_t)width(k) * 8, n,
+                                 cudaMemcpyHostToDevice, ctx->copy_stream[0]));
+            CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
+            return GLP_OK;
+        };
+        GLP(upload(0));
+        if (nblocks > 1) GLP(upload(1));
+        for (uint64_t k = 0; k < nblocks; k++) {
+            CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
+            sc.col0 = part_col0 + k * w;
+            GLP(lde_block(ctx, logN, logE, stage[k & 1], width(k), (gl_t *)ctx->work.p, width(k), width(k), &sc));
+            CU(cudaEventRecord(used[k], ctx->stream));
+            if (k + 2 < nblocks) GLP(upload(k + 2));
+        }
+        cudaError_t e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->copy_stream[0]);
+        for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(used[k]); }
+        cudaEventDestroy(start);
+        CU(e0); CU(e1);
+        return GLP_OK;
+    }
+    const uint32_t wb = pick_block_cols(ctx, n + n_ext, ncols);
+    GLP(ensure(ctx, ctx->work, (size_t)n_ext * wb * sizeof(gl_t)));
+    for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
+        const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+        sc.col0 = part_col0 + c0;
+        GLP(lde_block(ctx, logN, logE, (const gl_t *)in + c0, in_pitch, (gl_t *)ctx->work.p, w, w, &sc));
+    }
+    return GLP_OK;
+}
+
+extern "C" int glp_ipc_export(glp_ctx *ctx, void *devptr, unsigned char handle[64])
+{
+    if (!ctx || !devptr || !handle) return fail(GLP_E_ARG, "glp_ipc_export: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof h == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CU(cudaIpcGetMemHandle(&h, devptr));
+    memcpy(handle, &h, 64);
+    return GLP_OK;
+}
+extern "C" int glp_ipc_import(glp_ctx *ctx, const unsigned char handle[64], void **devptr)
+{
+    if (!ctx || !devptr || !handle) return fail(GLP_E_ARG, "glp_ipc_import: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    CU(cudaIpcOpenMemHandle(devptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return GLP_OK;
+}
+extern "C" int glp_ipc_close(glp_ctx *ctx, void *devptr)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (devptr) CU(cudaIpcCloseMemHandle(devptr));
     return GLP_OK;
 }
 

@@ -62,6 +62,12 @@ struct NttPass {
     uint32_t scatter;                // last DIF pass: store to the natural row index instead of in place
     uint32_t nprev, prev_log[NTT_MAX_PASSES - 1];   // tile sizes (log2) of the earlier passes, for the natural index
     uint32_t canon_in, canon_out;
+    // Row-sharded output (the multi-GPU exchange fused into the transform's last pass): when nparts > 0 output row r
+    // goes to parts[r >> log_part_rows] + (r & (2^log_part_rows - 1)) * part_pitch + part_col0 instead of `out`.  The
+    // part bases may be peer-GPU memory mapped over NVLink (cudaIpcOpenMemHandle); parts is a small device array.
+    const unsigned long long *parts;
+    uint32_t nparts, log_part_rows;
+    uint64_t part_pitch, part_col0;
 };
 
 static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
@@ -165,6 +171,16 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
         for (int w = 0; w < QX; w++) v[w] = gl_canon(v[w]);
     }
     if (!colok) return;
+    if (a.nparts) {                                              // scatter rows to the slabs of their owners
+        const uint64_t rmask = (1ull << a.log_part_rows) - 1;
+#pragma unroll
+        for (int w = 0; w < QX; w++) {
+            const uint64_t r = rbase + ((uint64_t)(t0 + (uint32_t)w * tstride) << rsh);
+            gl_t *base = (gl_t *)__ldg(a.parts + (r >> a.log_part_rows));
+            base[(r & rmask) * a.part_pitch + a.part_col0 + col] = v[ntt_slot<LOGX, INV>(w)];
+        }
+        return;
+    }
     gl_t *o = a.out + (rbase + ((uint64_t)t0 << rsh)) * a.out_pitch + col;
     const uint64_t step = ((uint64_t)tstride << rsh) * a.out_pitch;
 #pragma unroll
@@ -284,6 +300,18 @@ __global__ void k_ntt_copy_canon(gl_t *out, uint64_t out_pitch, const gl_t *in, 
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
         const uint64_t r = i / ncols, c = i % ncols;
         out[r * out_pitch + c] = gl_canon(in[r * in_pitch + c]);
+    }
+}
+
+// rows of a dense [nrows x ncols] block -> the slabs of their owners (fallback of the fused scatter)
+__global__ void k_ntt_scatter_rows(const unsigned long long *parts, uint32_t log_part_rows, uint64_t part_pitch, uint64_t part_col0,
+                                   const gl_t *in, uint64_t in_pitch, uint64_t nrows, uint64_t ncols)
+{
+    const uint64_t total = nrows * ncols, rmask = (1ull << log_part_rows) - 1;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / ncols, c = i % ncols;
+        gl_t *base = (gl_t *)__ldg(parts + (r >> log_part_rows));
+        base[(r & rmask) * part_pitch + part_col0 + c] = gl_canon(in[r * in_pitch + c]);
     }
 }
 

@@ -9,6 +9,10 @@ exactly as BASELINE.json's north_star prescribes:
      (all_to_all_single), and each rank interleaves what it received into a reference-layout
      [R x C] row slab of the extended matrix;
   3. rank j hashes its R leaf rows and builds its subtree (glp_merkletree on the slab);
+     With fused=True (the default on CUDA) steps 1 and 2 are ONE pass over the data: every rank maps its peers' row
+     slabs (CUDA IPC over NVLink) and the LDE's last NTT pass stores each tile straight into the owner's slab at this
+     rank's column offset (glp_extend_pol_scatter) -- no all-to-all, no receive buffer, no interleave pass; the only
+     collective left is a one-word all-reduce that orders the peers' stores before the hashing;
   4. the G subtrees are gathered on rank 0, re-laid level-major into the reference's `nodes` layout
      (poseidon_goldilocks.cpp:283-300) and the top log2(G) levels are hashed there (glp_merkle_levels).
 
@@ -51,7 +55,7 @@ class ShardedCommit:
     """commit(in_slice) for one rank.  `ctx` is this rank's glprover Context; `device` the torch device the
     buffers live on ('cuda:N', or 'cpu' with the emulator backend in the gloo tests)."""
 
-    def __init__(self, ctx, n, n_ext, ncols, group=None, device=None, alloc=None):
+    def __init__(self, ctx, n, n_ext, ncols, group=None, device=None, alloc=None, fused=None):
         self.ctx, self.n, self.n_ext, self.ncols = ctx, n, n_ext, ncols
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -65,6 +69,13 @@ class ShardedCommit:
         i64 = dict(dtype=torch.int64, device=self.device)
         # alloc(nwords) -> int64 tensor; the gloo tests pass one that carves "device" memory out of the emulator
         empty = alloc if alloc is not None else (lambda nwords: torch.empty(nwords, **i64))
+        self.fused = (self.device.type == "cuda" and self.world > 1) if fused is None else bool(fused)
+        if self.fused:
+            self._init_fused()
+            self.subtree = empty(tree_num_elements(self.R))
+            self._empty = empty
+            self.tree = None
+            return
         # buffer A holds my columns for all rows (LDE output), then -- after the exchange -- my rows for all
         # columns (the slab the Merkle stage reads); buffer B receives the all-to-all.  Peak = A + B.
         self.buf_a = empty(max(1, n_ext * self.w, self.R * ncols))
@@ -75,6 +86,34 @@ class ShardedCommit:
         self._empty = empty
         self.tree = None
 
+    def _init_fused(self):
+        """My row slab comes straight from cudaMalloc (so it can be exported), every peer's slab is mapped here."""
+        R, C, G = self.R, self.ncols, self.world
+        self.slab_ptr = self.ctx.device_alloc(8 * max(1, R * C))
+        self.slab = _tensor_from_ptr(self.slab_ptr, max(1, R * C), self.device)[: R * C]
+        handles = [None] * G
+        dist.all_gather_object(handles, self.ctx.ipc_export(self.slab_ptr), group=self.group)
+        self.parts = [self.slab_ptr if g == self.rank else self.ctx.ipc_import(handles[g]) for g in range(G)]
+        self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.ext_cols = self.recv = None
+
+    def close(self):
+        if getattr(self, "fused", False) and getattr(self, "parts", None):
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)           # nobody unmaps while a peer may still be storing
+            for g, p in enumerate(self.parts):
+                if g != self.rank:
+                    self.ctx.ipc_close(p)
+            self.slab = None
+            self.ctx.device_free(self.slab_ptr)
+            self.parts = None
+
+    def _fence(self):
+        """Stream-ordered rendezvous of all ranks (a one-word all-reduce): peers' stores before it are complete and visible after it."""
+        dist.all_reduce(self._flag, group=self.group)
+
     def bind_stream(self):
         """Launch the library's kernels on torch's current stream so they order with the collectives."""
         if self.device.type == "cuda":
@@ -82,12 +121,20 @@ class ShardedCommit:
 
     def extend(self, in_slice, in_pitch=None):
         """Step 1: LDE of my column slice.  in_slice: [n x w] (pitch in_pitch, default dense)."""
+        if self.fused:
+            self._fence()                       # every rank has finished reading its slab (the previous commit's hashing)
+            if self.w:
+                self.ctx.extend_pol_scatter(self.parts, self.ncols, self.c0, in_slice, in_pitch or self.w, self.n_ext, self.n, self.w)
+            return
         if self.w:
             self.ctx.extend_pol_pitched(self.ext_cols, self.w, in_slice, in_pitch or self.w, self.n_ext, self.n, self.w)
 
     def exchange(self):
         """Step 2: the one collective, then interleave into the row slab."""
         R, C, G = self.R, self.ncols, self.world
+        if self.fused:
+            self._fence()                       # all ranks' last-pass stores into my slab have landed
+            return
         if G == 1:
             return                              # slab and ext_cols are the same memory
         in_splits = [R * self.w] * G
@@ -133,7 +180,9 @@ class ShardedCommit:
         host_tree = pinned tensor for the whole tree (rank 0).  Uploads overlap the LDE column block by column block
         (glp_extend_pol's streamed path); the slab's download runs on a side stream while the leaves are hashed."""
         self.bind_stream()
-        if self.w:
+        if self.fused:
+            self.extend(host_in)                # glp_extend_pol_scatter streams a host input block by block
+        elif self.w:
             self.ctx.extend_pol(self.ext_cols, host_in, self.n_ext, self.n, self.w)
         self.exchange()
         cuda = self.device.type == "cuda"
@@ -157,6 +206,17 @@ class ShardedCommit:
             if host_ext is not None:
                 self._side.synchronize()
         return root
+
+
+class _CudaBuffer:
+    """A raw device allocation seen through __cuda_array_interface__, so that torch can view it as a tensor."""
+
+    def __init__(self, ptr, nwords):
+        self.__cuda_array_interface__ = {"shape": (nwords,), "typestr": "<i8", "data": (ptr, False), "version": 2}
+
+
+def _tensor_from_ptr(ptr, nwords, device):
+    return torch.as_tensor(_CudaBuffer(ptr, nwords), device=device)
 
 
 def to_numpy_u64(t):
