@@ -108,6 +108,10 @@ int glp_linear_hash_absorb(glp_ctx *ctx, uint64_t *state4, const uint64_t *in, u
  * tree = (2*nrows-1)*4 words, level-major, root last.  A row is ncols*dim words.  nrows must be a power of
  * two (the reference reads a neighbour's node otherwise; every caller passes powers of two). */
 int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t dim);
+/* merkletree_batch / _avx / _avx512 (poseidon_goldilocks.cpp:113-164, :302-352, :521-577): the leaf of a row is the
+ * linear_hash of the concatenated linear_hashes of its column batches (batch_size columns each, the last one shorter);
+ * the levels above are the same.  Not called by MerkleTreeGL / Starks; provided with its known answers. */
+int glp_merkletree_batch(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t batch_size, uint64_t dim);
 /* The level loop alone (poseidon_goldilocks.cpp:283-300): `level` holds n nodes (4 words each) followed by
  * room for the n-1 nodes above them.  Used for the top log2(G) levels of the multi-GPU tree. */
 int glp_merkle_levels(glp_ctx *ctx, uint64_t *level, uint64_t n);

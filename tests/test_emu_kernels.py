@@ -74,6 +74,22 @@ def test_linear_hash_and_tree(ectx, oracle, golden, fixtures, rng):
     check_equal(run_merkletree(ectx, a, dim=3), oracle.merkletree(a), "dim=3")
 
 
+def check_merkletree_batch(ctx, oracle, golden, rng):
+    a = fib_matrix(64, 128)
+    tree = np.zeros(tree_words(64), dtype=np.uint64)
+    ctx.merkletree_batch(tree, a, 128, 64, 32)
+    check_equal(tree[-4:], golden["merkletree_batch_64x128_b32_root"]["out"], "merkletree_batch KAT (tests.cpp:2021-2119)")
+    for nrows, ncols, batch in [(8, 37, 8), (4, 9, 16), (16, 12, 5), (2, 3, 2), (8, 64, 64)]:
+        a = edge_matrix(rng, nrows, ncols)
+        tree = np.zeros(tree_words(nrows), dtype=np.uint64)
+        ctx.merkletree_batch(tree, a, ncols, nrows, batch)
+        check_equal(tree, oracle.merkletree_batch(a, batch), "merkletree_batch %s" % ((nrows, ncols, batch),))
+
+
+def test_merkletree_batch(ectx, oracle, golden, rng):
+    check_merkletree_batch(ectx, oracle, golden, rng)
+
+
 def test_ntt_single_pass(ectx, oracle, fixtures, rng):
     for n, c in [(1, 3), (2, 3), (4, 1), (16, 8), (32, 5), (128, 2)]:
         check_ntt(ectx, oracle, edge_matrix(rng, n, c))

@@ -85,6 +85,15 @@ def test_merkletree_kats(ctx, golden):
     check_equal(run_merkletree(ctx, None, 1 << 17, 0)[-4:], golden["merkletree_131072x0_root"]["out"], "2^17x0")
 
 
+def test_merkletree_batch(ctx, oracle, golden, rng):
+    from test_emu_kernels import check_merkletree_batch
+    check_merkletree_batch(ctx, oracle, golden, rng)
+    a = edge_matrix(rng, 1 << 12, 128)
+    tree = np.zeros(tree_words(1 << 12), dtype=np.uint64)
+    ctx.merkletree_batch(tree, a, 128, 1 << 12, 32)
+    check_equal(tree, oracle.merkletree_batch(a, 32), "merkletree_batch 2^12 x 128, batch 32")
+
+
 def test_merkletree_fixtures(ctx, fixtures):
     for k in ("mt_32x13", "mt_16x4", "mt_16x3", "mt_8x8", "mt_4x660", "mt_1x9"):
         for dev in (False, True):
@@ -424,3 +433,61 @@ def test_large_merkle_paths(ctx, oracle):
         check_equal(h, nodes[-4:], "root from leaf %d" % idx)
     ctx.device_free(src)
     ctx.device_free(tree)
+
+
+# ---------------------------------------------------------------- full-size secondary shapes (BASELINE.json configs[2], FRI/cm4 widths)
+def _check_full_size_commit(ctx, oracle, logn, ncols, logb, seed, cols_to_check):
+    """Device-resident commit at full size; the oracle re-derives whole columns of the extension (it is column-wise
+    independent) and sampled Merkle paths (leaf = linear_hash of the row, then the sibling path up to the root)."""
+    from xlayer_prover_b200 import synth_matrix
+    n, ne = 1 << logn, 1 << (logn + logb)
+    src = ctx.device_alloc(n * ncols * 8)
+    ext = ctx.device_alloc(ne * ncols * 8)
+    tree = ctx.device_alloc(tree_words(ne) * 8)
+    ctx.synth_fill(src, n, ncols, seed)
+    root = ctx.commit(ext, tree, src, n, ne, ncols)
+    e = ctx.to_host(ext, (ne, ncols))
+    nodes = ctx.to_host(tree, (tree_words(ne),))
+    for c in cols_to_check:
+        a = synth_matrix(n, 1, seed, col0=c, ncols_total=ncols)
+        check_equal(e[:, c], oracle.extend_pol(a, ne)[:, 0], "2^%d x %d blowup %d, column %d" % (logn, ncols, 1 << logb, c))
+    depth = logn + logb
+    for idx in [0, ne - 1] + [int(r) for r in np.random.default_rng(5).integers(0, ne, size=10)]:
+        h = oracle.linear_hash(e[idx])
+        check_equal(nodes[4 * idx: 4 * idx + 4], h, "leaf %d" % idx)
+        off, nn, i = 0, ne, idx
+        for _ in range(depth):
+            sib = nodes[off + 4 * (i ^ 1): off + 4 * (i ^ 1) + 4]
+            pair = np.concatenate([h, sib]) if i % 2 == 0 else np.concatenate([sib, h])
+            h = oracle.hash_full_result(np.concatenate([pair, np.zeros(4, dtype=np.uint64)]))[:4]
+            off += 4 * nn
+            nn //= 2
+            i //= 2
+        check_equal(h, root, "path of leaf %d" % idx)
+    check_equal(nodes[-4:], root)
+    for p in (src, ext, tree):
+        ctx.device_free(p)
+
+
+def test_config_c_full_size(ctx, oracle):
+    """BASELINE.json configs[2]: 2^20 rows x 200 columns, blowup 8 (nBitsExt = 23)"""
+    _check_full_size_commit(ctx, oracle, 20, 200, 3, 0x9E3779B97F4A7C15 + 3, [0, 77, 199])
+
+
+@pytest.mark.parametrize("logn,ncols,logb", [(20, 1, 1), (20, 3, 2), (18, 6, 1), (17, 18, 3), (16, 12, 4)])
+def test_narrow_shapes_full_size(ctx, oracle, logn, ncols, logb):
+    """the narrow-matrix lane mapping (<= 16 columns: 32/cw tiles per warp) and the recursive-prover widths"""
+    _check_full_size_commit(ctx, oracle, logn, ncols, logb, 0xFACE + ncols, sorted(set([0, ncols - 1])))
+
+
+def test_narrow_equals_wide_mapping(ctx, rng):
+    """same transforms with GLP_NTT_NO_NARROW=1 (lane = column) must give identical bits"""
+    wide = env_ctx(GLP_NTT_NO_NARROW=1)
+    try:
+        for n, c in [(1 << 12, 1), (1 << 16, 3), (1 << 9, 16), (1 << 17, 5)]:
+            a = edge_matrix(rng, n, c)
+            for inv, ext in [(False, False), (True, False), (True, True)]:
+                check_equal(run_ntt(ctx, a, inv, ext), run_ntt(wide, a, inv, ext), "narrow vs wide %s inv=%d ext=%d" % ((n, c), inv, ext))
+            check_equal(run_extend(ctx, a, 4 * n), run_extend(wide, a, 4 * n), "narrow vs wide extend %s" % ((n, c),))
+    finally:
+        wide.close()

@@ -24,7 +24,7 @@ int main(int argc, char **argv)
     float best = 1e30f;
     for (int rep = 0; rep < 6; rep++) {
         cudaEventRecord(a);
-        k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0><<<nblk, POS_LEAF_BLOCK>>>(out, in, ncols, ncols, nrows, 1, nullptr);
+        k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0><<<nblk, POS_LEAF_BLOCK>>>(out, in, ncols, ncols, nrows, 1, nullptr, 4);
         cudaEventRecord(b);
         cudaEventSynchronize(b);
         float ms;

@@ -112,6 +112,14 @@ class PoseidonGoldilocks:
             return
         (ctx or default_context()).merkletree(tree, input, num_cols, num_rows, dim)
 
+    @staticmethod
+    def merkletree_batch(tree, input, num_cols, num_rows, batch_size, nThreads=0, dim=1, ctx=None):
+        """poseidon_goldilocks.hpp:44,82-88"""
+        if num_rows == 0:
+            return
+        (ctx or default_context()).merkletree_batch(tree, input, num_cols, num_rows, batch_size, dim)
+
+    merkletree_batch_avx = merkletree_batch_avx512 = merkletree_batch_seq = merkletree_batch
     merkletree_avx = merkletree
     merkletree_avx512 = merkletree
     merkletree_seq = merkletree

@@ -46,6 +46,7 @@ SIGNATURES = {
     "glp_linear_hash_rows": (i32, [vp, vp, vp, u64, u64, u64]),
     "glp_linear_hash_absorb": (i32, [vp, vp, vp, u64, u64, u64, i32]),
     "glp_merkletree": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_merkletree_batch": (i32, [vp, vp, vp, u64, u64, u64, u64]),
     "glp_merkle_levels": (i32, [vp, vp, u64]),
     "glp_tree_num_elements": (u64, [u64]),
     "glp_merkle_group_proof": (i32, [vp, vp, vp, vp, u64, u64, u64]),
@@ -214,6 +215,9 @@ class Context:
 
     def merkletree(self, tree, inp, ncols, nrows, dim=1):
         self.lib.check(self.lib.glp_merkletree(self.h, ptr_of(tree), ptr_of(inp), ncols, nrows, dim))
+
+    def merkletree_batch(self, tree, inp, ncols, nrows, batch_size, dim=1):
+        self.lib.check(self.lib.glp_merkletree_batch(self.h, ptr_of(tree), ptr_of(inp), ncols, nrows, batch_size, dim))
 
     def merkle_levels(self, level, n):
         self.lib.check(self.lib.glp_merkle_levels(self.h, ptr_of(level), n))

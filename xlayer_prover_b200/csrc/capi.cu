@@ -53,6 +53,7 @@ struct glp_ctx {
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
+    bool no_narrow = false;                  // GLP_NTT_NO_NARROW=1: lane = column even for matrices of <= 16 columns (comparison runs)
     bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
     std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
     std::map<uint32_t, TwoLevel> sc_tabs;    // shift^j / N, by logN
@@ -149,6 +150,8 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_pass_tables = npt && atoi(npt) != 0;
     const char *nfl = getenv("GLP_NTT_NO_FUSED_LDE");
     ctx->no_fused_lde = nfl && atoi(nfl) != 0;
+    const char *nn = getenv("GLP_NTT_NO_NARROW");
+    ctx->no_narrow = nn && atoi(nn) != 0;
     const char *tr = getenv("GLP_TRACE");
     ctx->trace = tr && atoi(tr) != 0;
     const char *sc = getenv("GLP_STREAM_COLS");
@@ -361,19 +364,36 @@ static int get_scale_table(glp_ctx *ctx, uint32_t logN, const NttPlanLogs &pl, c
     return GLP_OK;
 }
 
+#define NTT_NARROW_MAX_COLS 16
 template <int A, int B>
-static int launch_pass_ab(glp_ctx *ctx, const NttPass &a, bool inv, uint32_t lsh)
+static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t lsh)
 {
+    NttPass a = a_in;
+    const bool narrow = a.ncols <= NTT_NARROW_MAX_COLS && !ctx->no_narrow;
     const uint64_t ntiles = 1ull << (a.logN - (A + B));
-    const uint64_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
-    const uint64_t grid = (B == 0 ? (ntiles + NTT_WARPS - 1) / NTT_WARPS : ntiles) * ncg;
+    uint64_t grid;
+    if (narrow) {
+        a.log_cw = 0;
+        while ((1u << a.log_cw) < a.ncols) a.log_cw++;
+        const uint64_t tiles_per_warp = 32u >> a.log_cw;
+        const uint64_t groups = (ntiles + tiles_per_warp - 1) / tiles_per_warp;          // warps' worth of tiles
+        grid = B == 0 ? (groups + NTT_WARPS - 1) / NTT_WARPS : groups;
+    } else {
+        const uint64_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
+        grid = (B == 0 ? (ntiles + NTT_WARPS - 1) / NTT_WARPS : ntiles) * ncg;
+    }
     if (grid > 0x7FFFFFFFull) return fail(GLP_E_ARG, "NTT grid too large");
     const size_t smem = B == 0 ? 0 : ((size_t)1 << (A + B)) * NTT_LANES * sizeof(gl_t);
-#define NTT_GO(INV, LSH)                                                             \
+#define NTT_GO2(INV, LSH, NARROW)                                                    \
     do {                                                                             \
-        auto kfn = k_ntt_pass<A, B, INV, LSH>;                                       \
+        auto kfn = k_ntt_pass<A, B, INV, LSH, NARROW>;                               \
         if (smem > 48 * 1024) GLP_SET_SMEM(kfn, smem);                               \
         LAUNCH(ctx, kfn, (unsigned)grid, NTT_THREADS, smem, a);                      \
+    } while (0)
+#define NTT_GO(INV, LSH)                                                             \
+    do {                                                                             \
+        if (narrow) NTT_GO2(INV, LSH, true);                                         \
+        else NTT_GO2(INV, LSH, false);                                               \
     } while (0)
     if (inv) NTT_GO(true, 0);
     else if (A == 4 && lsh == 1) NTT_GO(false, (A == 4 ? 1 : 0));
@@ -381,6 +401,7 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a, bool inv, uint32_t lsh
     else if (A == 4 && lsh == 3) NTT_GO(false, (A == 4 ? 3 : 0));
     else NTT_GO(false, 0);
 #undef NTT_GO
+#undef NTT_GO2
     return GLP_OK;
 }
 static int launch_pass(glp_ctx *ctx, const NttPass &a, uint32_t lg, bool inv, uint32_t lsh)
@@ -855,13 +876,14 @@ extern "C" int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, u
 // ------------------------------------------------------------------------------------------------
 extern "C" uint64_t glp_tree_num_elements(uint64_t nrows) { return nrows ? (2 * nrows - 1) * 4 : 0; }
 
-static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows, const gl_t *cap_in = nullptr)
+static int dev_leaf_hash(glp_ctx *ctx, gl_t *out4, const gl_t *in, uint64_t ncols, uint64_t pitch, uint64_t nrows, const gl_t *cap_in = nullptr,
+                         uint64_t out_pitch = 4)
 {
     if (!nrows) return GLP_OK;
     const int vec16 = (pitch % 2 == 0) && (((uintptr_t)in) % 16 == 0);
     const uint64_t nblk = (nrows + POS_LEAF_BLOCK - 1) / POS_LEAF_BLOCK;
     if (nblk > 0x7FFFFFFFull) return fail(GLP_E_ARG, "too many rows");
-    LAUNCH_FLAT(ctx, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>, (unsigned)nblk, POS_LEAF_BLOCK, out4, in, ncols, pitch, nrows, vec16, cap_in);
+    LAUNCH_FLAT(ctx, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>, (unsigned)nblk, POS_LEAF_BLOCK, out4, in, ncols, pitch, nrows, vec16, cap_in, out_pitch);
     CU(cudaGetLastError());
     return GLP_OK;
 }
@@ -967,6 +989,42 @@ extern "C" int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, 
     gl_t *dtree = (gl_t *)tree;
     if (!out_dev) { GLP(ensure(ctx, ctx->nodes, tw * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
     GLP(dev_merkletree(ctx, dtree, din, width, width, nrows));
+    if (!out_dev) CU(cudaMemcpyAsync(tree, dtree, tw * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+extern "C" int glp_merkletree_batch(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t batch_size,
+                                    uint64_t dim)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (nrows == 0) return GLP_OK;                                  // poseidon_goldilocks.cpp:115-118
+    const uint64_t width = ncols * dim;
+    if (!tree || (!in && width)) return fail(GLP_E_ARG, "glp_merkletree_batch: NULL pointer");
+    if (!is_pow2(nrows)) return fail(GLP_E_ARG, "glp_merkletree_batch: nrows must be a power of two");
+    if (batch_size == 0) return fail(GLP_E_ARG, "glp_merkletree_batch: batch_size is 0");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t nb = ncols ? (ncols + batch_size - 1) / batch_size : 1;      // :121-126
+    const uint64_t nlast = ncols - (nb - 1) * batch_size;
+    const size_t tw = glp_tree_num_elements(nrows);
+    const gl_t *din = (const gl_t *)in;
+    if (width) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)nrows * width, &din));
+    const bool out_dev = on_device(tree);
+    gl_t *dtree = (gl_t *)tree;
+    if (!out_dev) { GLP(ensure(ctx, ctx->nodes, tw * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+    // per-batch hashes side by side: [nrows x 4*nb], then one more linear_hash over each of those rows (:131-141)
+    GLP(ensure(ctx, ctx->tmp_out, (size_t)nrows * 4 * nb * sizeof(gl_t)));
+    gl_t *bh = (gl_t *)ctx->tmp_out.p;
+    {
+        ProfScope ps(ctx, 2);
+        for (uint64_t j = 0; j < nb; j++)
+            GLP(dev_leaf_hash(ctx, bh + 4 * j, din + j * batch_size * dim, (j == nb - 1 ? nlast : batch_size) * dim, width, nrows, nullptr, 4 * nb));
+        GLP(dev_leaf_hash(ctx, dtree, bh, 4 * nb, 4 * nb, nrows));
+    }
+    {
+        ProfScope ps(ctx, 3);
+        GLP(dev_tree_levels(ctx, dtree, nrows));
+    }
     if (!out_dev) CU(cudaMemcpyAsync(tree, dtree, tw * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return GLP_OK;

@@ -68,6 +68,7 @@ struct NttPass {
     const unsigned long long *parts;
     uint32_t nparts, log_part_rows;
     uint64_t part_pitch, part_col0;
+    uint32_t log_cw;                 // NARROW kernels: lanes per tile = 2^log_cw >= ncols (32 >> log_cw tiles share a warp)
 };
 
 static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
@@ -190,7 +191,11 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
 // One tile pass.  A, B: log2 radix of the two in-register steps (B == 0: single step, no shared memory).
 // grid.x = tiles * ceil(ncols / 32) (column group fastest, so neighbouring CTAs touch neighbouring segments of
 // the same rows); B == 0 packs NTT_WARPS tiles into a CTA.
-template <int A, int B, bool INV, int LSH>
+// NARROW (matrices of <= 16 columns: FRI polynomials, the cm4 quotient, single-column transforms): a warp's 32 lanes
+// are shared by 32/cw neighbouring tiles of cw = 2^log_cw >= ncols lanes each.  Neighbouring tiles are neighbouring rows
+// p, p+1, ..., so a warp still touches one contiguous run of memory per access; the tile index, and with it the twiddle
+// row, becomes a per-lane quantity instead of a warp-uniform one.  Everything else is the same code.
+template <int A, int B, bool INV, int LSH, bool NARROW>
 __global__ void __launch_bounds__(NTT_THREADS, 2)
 k_ntt_pass(NttPass a)
 {
@@ -199,16 +204,17 @@ k_ntt_pass(NttPass a)
     const uint32_t lane = threadIdx.x % NTT_LANES, warp = threadIdx.x / NTT_LANES;
     const uint32_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
     const uint64_t ntiles = 1ull << (a.logN - LOGQ);
-    const uint32_t cg = blockIdx.x % ncg;
-    uint64_t tix = blockIdx.x / ncg;
-    if (B == 0) {
-        tix = tix * NTT_WARPS + warp;
-        if (tix >= ntiles) return;                               // no barrier in the single-step kernel
-    }
+    const uint32_t cg = NARROW ? 0 : blockIdx.x % ncg;
+    uint64_t tix = NARROW ? blockIdx.x : blockIdx.x / ncg;
+    if (B == 0) tix = tix * NTT_WARPS + warp;
+    if (NARROW) tix = (tix << (5 - a.log_cw)) + (lane >> a.log_cw);
+    bool tileok = tix < ntiles;
+    if (B == 0 && !NARROW && !tileok) return;                    // no barrier in the single-step kernel
+    if (!tileok) tix = 0;                                        // idle lanes of a partly filled narrow warp compute on tile 0 and store nothing
     const uint32_t logS = a.logL - LOGQ;
     const uint64_t p = tix & ((1ull << logS) - 1), bb = tix >> logS;
-    const uint32_t col = cg * NTT_LANES + lane;
-    const bool colok = col < a.ncols;
+    const uint32_t col = NARROW ? (lane & ((1u << a.log_cw) - 1)) : cg * NTT_LANES + lane;
+    const bool colok = col < a.ncols && tileok;
     const gl_t *twp = a.tw ? a.tw + (p << LOGQ) : nullptr;
     const uint64_t posbase = (bb << a.logL) + p;
     // natural index of tile output t: kbase + (t << ksh); digit k_i of pass i has weight Q_0...Q_(i-1)
@@ -229,14 +235,14 @@ k_ntt_pass(NttPass a)
     const gl_t *fptr = nullptr;
     uint32_t fsh = 0, fkind = 0, fbsh = 0;
     uint64_t fbase = 0;
-    if (a.tw_mode == NTT_TW_POST && p != 0) { omul = true; fptr = twp; fkind = INV ? NTT_F_TW_INV : NTT_F_TW; }
+    if (a.tw_mode == NTT_TW_POST && (NARROW || p != 0)) { omul = true; fptr = twp; fkind = INV ? NTT_F_TW_INV : NTT_F_TW; }   // row p = 0 of the table is all ones
     else if (a.scale_mode == NTT_SC_CONST) { omul = true; fkind = NTT_F_CONST; }
     else if (a.scale_mode == NTT_SC_TABLE) { omul = true; fptr = a.sc + posbase; fsh = logS; }
     else if (a.scale_mode == NTT_SC_TWOLEVEL) { omul = true; fkind = NTT_F_SCALE2; fbase = kbase; fbsh = ksh; }
     const uint64_t rbase = a.scatter ? kbase : posbase;
     const uint32_t rsh = a.scatter ? ksh : logS;
     const uint64_t in_step = ((uint64_t)QB << logS) * a.in_pitch;   // between consecutive high digits m of q = m*QB + b
-    const bool pre = a.tw_mode == NTT_TW_PRE && p != 0;
+    const bool pre = a.tw_mode == NTT_TW_PRE && (NARROW || p != 0);
     const NttSlow sl = {a.tw_lo, a.tw_hi, a.sc_lo, a.sc_hi, a.scale_const, a.logN, a.logL};
 
     // ---- step 1: 2^A-point transforms over the high digit of q = m*QB + b ----

@@ -48,7 +48,8 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 // last row and simply not stored), so the per-round barriers inside pos_permute_t are reached by all.
 template <bool LOCKSTEP>
 __global__ void __launch_bounds__(POS_LEAF_BLOCK)
-k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in)
+k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in,
+                   uint64_t out_pitch)
 {
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = row < nrows;
@@ -57,7 +58,7 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
         row = nrows - 1;
     }
     const gl_t *p = in + row * pitch;
-    gl_t *o = out + row * 4;
+    gl_t *o = out + row * out_pitch;                  // 4 for a tree's leaf array; wider when the hashes of several column batches sit side by side
     if (ncols <= POS_CAP && !cap_in) {            // size <= CAPACITY: copy and zero-pad, no hashing (:234-239)
         if (live) {
 #pragma unroll
@@ -70,7 +71,7 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     uint64_t nblk = (ncols + 7) / 8;
     pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16 != 0);
 #pragma unroll
-    for (int i = 8; i < 12; i++) x[i] = cap_in ? cap_in[row * 4 + (i - 8)] : 0;   // capacity starts at zero (:243-246)
+    for (int i = 8; i < 12; i++) x[i] = cap_in ? cap_in[row * out_pitch + (i - 8)] : 0;   // capacity starts at zero (:243-246)
 #pragma unroll 1
     for (uint64_t b = 0; b < nblk; b++) {
 #pragma unroll
