@@ -80,6 +80,8 @@ cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size
 cudaError_t cudaMemset(void *d, int v, size_t n);
 cudaError_t cudaMemsetAsync(void *d, int v, size_t n, cudaStream_t st);
 cudaError_t cudaStreamCreateWithFlags(cudaStream_t *s, unsigned flags);
+static inline cudaError_t cudaStreamCreateWithPriority(cudaStream_t *s, unsigned flags, int) { return cudaStreamCreateWithFlags(s, flags); }
+static inline cudaError_t cudaDeviceGetStreamPriorityRange(int *lo, int *hi) { *lo = 0; *hi = -1; return cudaSuccess; }
 cudaError_t cudaStreamDestroy(cudaStream_t s);
 cudaError_t cudaStreamSynchronize(cudaStream_t s);
 cudaError_t cudaStreamWaitEvent(cudaStream_t s, cudaEvent_t e, unsigned flags);

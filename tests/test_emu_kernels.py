@@ -230,6 +230,24 @@ def test_commit_streamed_short_first_block(emu_lib, oracle, rng):
     c.close()
 
 
+def test_commit_overlapped(emu_lib, oracle, rng):
+    """device-resident commit as a pipeline of column blocks: LDE of block k+1 (k_ntt_pass_co, a small grid that walks
+    the tiles) on the high-priority stream, sponge absorption of block k on the caller's stream.  328 columns in blocks
+    of 8 (short first), 160, 160: five column groups per pass on the emulator's four "SMs", so CTAs take several turns."""
+    env = {"GLP_CO_COLS": "160", "GLP_CO_FIRST": "8", "GLP_CO": "1"}
+    os.environ.update(env)
+    try:
+        c = make_ctx(emu_lib)
+    finally:
+        for k in env:
+            os.environ.pop(k, None)
+    a = edge_matrix(rng, 128, 328)
+    launches0 = c.launch_count()
+    check_commit(c, oracle, a, 256, device=True)
+    assert c.launch_count() - launches0 >= 3 * 2 + 3      # one INTT + one NTT pass and one absorption per block, plus the levels
+    c.close()
+
+
 def test_argument_errors(ectx):
     from xlayer_prover_b200._capi import GLP_E_ARG, GLP_E_DOMAIN, GlpError
     a = np.zeros((12, 2), dtype=np.uint64)

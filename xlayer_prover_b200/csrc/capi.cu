@@ -47,6 +47,13 @@ struct glp_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
     cudaStream_t copy_stream[2] = {nullptr, nullptr};
+    cudaStream_t lde_stream = nullptr;       // high priority: the LDE of column block k+1 under the leaf hash of block k (commit_overlapped)
+    // co-resident NTT passes (k_ntt_pass_co): > 0 while the launches of an LDE should use the small resident grid
+    uint32_t co_active = 0;
+    uint32_t co_threads = 256, co_ctas_per_sm = 1;   // GLP_CO_THREADS, GLP_CO_CTAS
+    uint32_t co_cols = 96, co_first_cols = 32;       // GLP_CO_COLS, GLP_CO_FIRST: column-block widths of the overlapped commit
+    int co_mode = 0;                         // GLP_CO: 0 = stages back to back (default: measured fastest, profiles/r01_overlap_experiment.txt), 1 = LDE(k+1) under hash(k) with the co-resident kernels, 2 = same with the full-size kernels
+    int sm_count = 148;
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
     uint64_t stream_cols = 96;               // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
@@ -144,6 +151,20 @@ extern "C" int glp_init(int device, glp_ctx **out)
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[0], cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[1], cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
+    {
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&ctx->lde_stream, cudaStreamNonBlocking, hi));
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, device) == cudaSuccess && prop.multiProcessorCount > 0) ctx->sm_count = prop.multiProcessorCount;
+        else cudaGetLastError();
+        const char *e;
+        if ((e = getenv("GLP_CO"))) ctx->co_mode = atoi(e);
+        if ((e = getenv("GLP_CO_THREADS")) && atoi(e) >= 32 && atoi(e) <= NTT_THREADS) ctx->co_threads = (uint32_t)(atoi(e) / 32) * 32;
+        if ((e = getenv("GLP_CO_CTAS")) && atoi(e) >= 1 && atoi(e) <= 8) ctx->co_ctas_per_sm = (uint32_t)atoi(e);
+        if ((e = getenv("GLP_CO_COLS")) && atoi(e) >= 8) ctx->co_cols = (uint32_t)(atoi(e) / 8) * 8;
+        if ((e = getenv("GLP_CO_FIRST")) && atoi(e) >= 0) ctx->co_first_cols = (uint32_t)(atoi(e) / 8) * 8;
+    }
     const char *mq = getenv("GLP_NTT_MAX_LOGQ");
     if (mq && atoi(mq) >= 1 && atoi(mq) <= NTT_MAX_LOGQ) ctx->max_logq = (uint32_t)atoi(mq);
     const char *npt = getenv("GLP_NTT_NO_PASS_TABLES");
@@ -171,6 +192,7 @@ extern "C" void glp_destroy(glp_ctx *ctx)
     cudaStreamDestroy(ctx->own_stream);
     cudaStreamDestroy(ctx->copy_stream[0]);
     cudaStreamDestroy(ctx->copy_stream[1]);
+    cudaStreamDestroy(ctx->lde_stream);
     delete ctx;
 }
 
@@ -390,9 +412,19 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t 
         if (smem > 48 * 1024) GLP_SET_SMEM(kfn, smem);                               \
         LAUNCH(ctx, kfn, (unsigned)grid, NTT_THREADS, smem, a);                      \
     } while (0)
+#define NTT_GO_CO(INV, LSH)                                                          \
+    do {                                                                             \
+        if constexpr (B > 0 && A + B >= 7) {                                         \
+            auto kfn = k_ntt_pass_co<A, B, INV, LSH>;                                \
+            if (smem > 48 * 1024) GLP_SET_SMEM(kfn, smem);                           \
+            const uint64_t cog = (uint64_t)ctx->sm_count * ctx->co_ctas_per_sm;      \
+            LAUNCH(ctx, kfn, (unsigned)(grid < cog ? grid : cog), ctx->co_threads, smem, a, (uint32_t)grid); \
+        }                                                                            \
+    } while (0)
 #define NTT_GO(INV, LSH)                                                             \
     do {                                                                             \
         if (narrow) NTT_GO2(INV, LSH, true);                                         \
+        else if (B > 0 && A + B >= 7 && ctx->co_active) NTT_GO_CO(INV, LSH);         \
         else NTT_GO2(INV, LSH, false);                                               \
     } while (0)
     if (inv) NTT_GO(true, 0);
@@ -401,6 +433,7 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t 
     else if (A == 4 && lsh == 3) NTT_GO(false, (A == 4 ? 3 : 0));
     else NTT_GO(false, 0);
 #undef NTT_GO
+#undef NTT_GO_CO
 #undef NTT_GO2
     return GLP_OK;
 }
@@ -1208,6 +1241,70 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     return GLP_OK;
 }
 
+// Device-resident commit with the two stages overlapped ON THE SAME SMs.  The leaf hash is bound by the multiplier pipes
+// (IMAD.WIDE / DFMA) and leaves ~40 % of the issue slots and of the ALU pipe idle; the NTT passes are bound by the ALU
+// pipe and use the multiplier lightly.  So the matrix is cut into column blocks (multiples of 8 columns:
+// whole sponge blocks), the main stream absorbs block k into every row's sponge (the leaf array is the sponge state,
+// glp_linear_hash_absorb) while a high-priority stream extends block k+1 with k_ntt_pass_co -- a small grid that is
+// resident next to the hash CTAs.  Block 0 is short and extended with the full-size kernels (nothing to hide it under).
+static int commit_overlapped(glp_ctx *ctx, gl_t *dext, gl_t *dtree, const gl_t *in, uint64_t n, uint64_t n_ext, uint64_t ncols)
+{
+    const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
+    std::vector<uint64_t> col0;
+    {
+        uint64_t c = 0;
+        col0.push_back(0);
+        if (ctx->co_first_cols && ncols > 2 * (uint64_t)ctx->co_first_cols) { c = ctx->co_first_cols; col0.push_back(c); }
+        const uint64_t rest = ncols - c, wmax = ctx->co_cols;
+        const uint64_t nb = (rest + wmax - 1) / wmax;
+        const uint64_t units = (rest + 7) / 8;                               // equal blocks, in units of 8 columns
+        for (uint64_t k = 0; k < nb; k++) {
+            const uint64_t u = units / nb + (k < units % nb ? 1 : 0);
+            c += u * 8;
+            col0.push_back(c < ncols ? c : ncols);
+        }
+        col0.back() = ncols;
+    }
+    const uint64_t nblocks = col0.size() - 1;
+    uint64_t wmaxb = 0;
+    for (uint64_t k = 0; k < nblocks; k++) wmaxb = (col0[k + 1] - col0[k] > wmaxb) ? col0[k + 1] - col0[k] : wmaxb;
+    GLP(ensure(ctx, ctx->s2, (size_t)n * wmaxb * sizeof(gl_t)));              // before the streams fork: no allocation inside the pipeline
+    cudaStream_t main_stream = ctx->stream;
+    cudaEvent_t start, done;
+    std::vector<cudaEvent_t> ext_done(nblocks);
+    CU(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    for (auto &e : ext_done) CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CU(cudaEventRecord(start, main_stream));
+    CU(cudaStreamWaitEvent(ctx->lde_stream, start, 0));
+    int rc = GLP_OK;
+    for (uint64_t k = 0; k < nblocks && rc == GLP_OK; k++) {
+        const uint64_t c0 = col0[k];
+        const uint32_t wk = (uint32_t)(col0[k + 1] - c0);
+        ctx->stream = ctx->lde_stream;                                         // the launches of lde_block go to the high-priority stream
+        ctx->co_active = (k > 0 && ctx->co_mode == 1) ? 1 : 0;
+        rc = lde_block(ctx, logN, logE, in + c0, ncols, dext + c0, ncols, wk);
+        ctx->co_active = 0;
+        ctx->stream = main_stream;
+        if (rc != GLP_OK) break;
+        CU(cudaEventRecord(ext_done[k], ctx->lde_stream));
+        CU(cudaStreamWaitEvent(main_stream, ext_done[k], 0));
+        ProfScope ps(ctx, 2);
+        rc = dev_leaf_hash(ctx, dtree, dext + c0, wk, ncols, n_ext, k == 0 ? nullptr : dtree);
+    }
+    if (rc == GLP_OK) {
+        ProfScope ps(ctx, 3);
+        rc = dev_tree_levels(ctx, dtree, n_ext);
+    }
+    // the caller's stream also covers whatever is left on the LDE stream (nothing, unless a launch failed half way)
+    cudaEventRecord(done, ctx->lde_stream);
+    cudaStreamWaitEvent(main_stream, done, 0);
+    cudaEventDestroy(start);
+    cudaEventDestroy(done);
+    for (auto &e : ext_done) cudaEventDestroy(e);
+    return rc;
+}
+
 extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in, uint64_t n,
                           uint64_t n_ext, uint64_t ncols)
 {
@@ -1228,10 +1325,17 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
     // device-resident input: the extended matrix lives on the device for the Merkle stage
     gl_t *dext = (gl_t *)out_ext;
     if (!ext_dev) { GLP(ensure(ctx, ctx->ext, ext_words * sizeof(gl_t))); dext = (gl_t *)ctx->ext.p; }
-    GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
-    if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     (void)in_words;
-    if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+    // overlap the stages when the matrix is wide enough for a pipeline of column blocks and the LDE has a fused plan
+    const bool overlap = want_tree && ctx->co_mode != 0 && !ctx->no_fused_lde && ncols >= 2 * (uint64_t)ctx->co_cols && dext != (const gl_t *)in;
+    if (overlap) {
+        GLP(commit_overlapped(ctx, dext, dtree, (const gl_t *)in, n, n_ext, ncols));
+        if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    } else {
+        GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
+        if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+        if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+    }
     if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));

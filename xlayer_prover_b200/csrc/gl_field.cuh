@@ -180,6 +180,50 @@ GL_HD gl_t gl_reduce128_t(gl_t lo, gl_t hi)
 }
 GL_HD gl_t gl_reduce128(gl_t lo, gl_t hi) { return gl_reduce128_t<GL_EPS_ALU != 0>(lo, hi); }
 
+// The same fold with ONE IMAD.WIDE on the multiplier pipe (4 cycles) instead of the IMAD.LO + IMAD.HI pair (6):
+//     u = p2*EPS + (EPS - p3)            no overflow: (p2 + 1)*EPS <= 2^64 - 2^32, and u >= 0
+//     t = (p1:p0) + u, carry c           value = t + c*2^64 - EPS  =  c ? t : t - EPS  (mod p)
+//     r = c ? t : t - EPS, and once more - EPS when that borrows (then r >= 2^64 - 2*EPS, no third wrap)
+// One ALU instruction more than gl_reduce128_t<false>; for kernels bound by the multiplier pipes (Poseidon).
+#if defined(__CUDACC__) && !defined(GLP_EMU)
+// EPS as a value ptxas cannot see: with the literal it rewrites p2 * 0xffffffff as a negate + IMAD.HI (6 cycles again);
+// read from the constant bank the product stays one IMAD.WIDE with a c[][] operand
+static __constant__ uint32_t GL_EPS_OPAQUE = 0xffffffffu;
+#endif
+GL_HD gl_t gl_reduce128_wide(gl_t lo, gl_t hi)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 p0,p1,p2,p3,u0,u1,m;\n\t"
+        "mov.b64 {p0,p1}, %1;\n\t"
+        "mov.b64 {p2,p3}, %2;\n\t"
+        "not.b32 p3, p3;\n\t"                         // EPS - p3
+        "mad.lo.cc.u32 u0, p2, %3, p3;\n\t"
+        "madc.hi.u32 u1, p2, %3, 0;\n\t"
+        "add.cc.u32 p0, p0, u0;\n\t"
+        "addc.cc.u32 p1, p1, u1;\n\t"
+        "addc.u32 m, 0xffffffff, 0;\n\t"              // EPS when there was NO carry, else 0
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.cc.u32 p1, p1, 0;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                       // 0xffffffff on borrow
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        "mov.b64 %0, {p0,p1};\n\t"
+        "}" : "=l"(r) : "l"(lo), "l"(hi), "r"(GL_EPS_OPAQUE));
+    return r;
+#else
+    return gl_reduce128_t<false>(lo, hi);
+#endif
+}
+// MODE 0: p2*EPS as IMAD.LO + IMAD.HI; 1: on the ALU pipe; 2: one IMAD.WIDE (gl_reduce128_wide)
+template <int MODE>
+GL_HD gl_t gl_reduce128_m(gl_t lo, gl_t hi)
+{
+    if (MODE == 2) return gl_reduce128_wide(lo, hi);
+    return gl_reduce128_t<MODE == 1>(lo, hi);
+}
+
 // full 64x64 -> 128 product as 32-bit limbs (4 IMAD.WIDE.U32)
 GL_HD void gl_mul_wide(gl_t a, gl_t b, gl_t &lo, gl_t &hi)
 {
@@ -209,6 +253,45 @@ GL_HD void gl_mul_wide(gl_t a, gl_t b, gl_t &lo, gl_t &hi)
     lo = (gl_t)w;
     hi = (gl_t)(w >> 64);
 #endif
+}
+
+// The same product as FOUR IMAD.WIDE (16 multiplier-pipe cycles instead of 18): no partial sum can overflow 64 bits,
+//     Z = a0*b0;  X = a0*b1 + z1;  W = a1*b0 + x0;  Y = a1*b1 + (x1 + w1);   product = Y : w0 : z0
+// ((2^32-1)^2 + 2^33 - 2 < 2^64), so no carry-out of a multiply is needed; the price is ALU moves that build the
+// zero-extended 64-bit addends.
+GL_HD void gl_mul_wide4(gl_t a, gl_t b, gl_t &lo, gl_t &hi)
+{
+#if GL_DEVICE_PTX
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,z0,z1,x0,x1,w0,w1,t0,t1,y0,y1;\n\t"
+        ".reg .u64 Z;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "mul.wide.u32 Z, a0, b0;\n\t"
+        "mov.b64 {z0,z1}, Z;\n\t"
+        "mad.lo.cc.u32 x0, a0, b1, z1;\n\t"         // the lo.cc / hi pair with one addend is what ptxas keeps as a single
+        "madc.hi.u32 x1, a0, b1, 0;\n\t"            // IMAD.WIDE with a 64-bit addend (a mad.wide.u32 gets its add split off)
+        "mad.lo.cc.u32 w0, a1, b0, x0;\n\t"
+        "madc.hi.u32 w1, a1, b0, 0;\n\t"
+        "add.cc.u32 t0, x1, w1;\n\t"
+        "addc.u32 t1, 0, 0;\n\t"
+        "mad.lo.cc.u32 y0, a1, b1, t0;\n\t"
+        "madc.hi.u32 y1, a1, b1, t1;\n\t"
+        "mov.b64 %0, {z0,w0};\n\t"
+        "mov.b64 %1, {y0,y1};\n\t"
+        "}" : "=l"(lo), "=l"(hi) : "l"(a), "l"(b));
+#else
+    gl_mul_wide(a, b, lo, hi);
+#endif
+}
+// multiply / square with the product form (W4: four IMAD.WIDE) and the fold (MODE, see gl_reduce128_m) chosen by the caller
+template <int MODE, bool W4>
+GL_HD gl_t gl_mul_m(gl_t a, gl_t b)
+{
+    gl_t lo, hi;
+    if (W4) gl_mul_wide4(a, b, lo, hi);
+    else gl_mul_wide(a, b, lo, hi);
+    return gl_reduce128_m<MODE>(lo, hi);
 }
 
 GL_HD gl_t gl_mul(gl_t a, gl_t b)
@@ -261,6 +344,22 @@ GL_HD gl_t gl_sqr(gl_t a)
     gl_t lo, hi;
     gl_sqr_wide(a, lo, hi);
     return gl_reduce128(lo, hi);
+}
+
+template <int MODE>
+GL_HD gl_t gl_sqr_m(gl_t a)
+{
+    gl_t lo, hi;
+    gl_sqr_wide(a, lo, hi);
+    return gl_reduce128_m<MODE>(lo, hi);
+}
+template <int MODE, bool W4>
+GL_HD gl_t gl_pow7_m(gl_t x)
+{
+    gl_t x2 = gl_sqr_m<MODE>(x);
+    gl_t x3 = gl_mul_m<MODE, W4>(x, x2);
+    gl_t x4 = gl_sqr_m<MODE>(x2);
+    return gl_mul_m<MODE, W4>(x3, x4);
 }
 
 // x^7, the Poseidon S-box (poseidon_goldilocks.hpp:91-97): 4 multiplies

@@ -195,17 +195,17 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
 // are shared by 32/cw neighbouring tiles of cw = 2^log_cw >= ncols lanes each.  Neighbouring tiles are neighbouring rows
 // p, p+1, ..., so a warp still touches one contiguous run of memory per access; the tile index, and with it the twiddle
 // row, becomes a per-lane quantity instead of a warp-uniform one.  Everything else is the same code.
+// The body works on the tile(s) of virtual block index vbx with `nwarps` warps (k_ntt_pass: vbx = blockIdx.x, 16 warps;
+// k_ntt_pass_co: a small resident grid walks the block indices, see below).
 template <int A, int B, bool INV, int LSH, bool NARROW>
-__global__ void __launch_bounds__(NTT_THREADS, 2)
-k_ntt_pass(NttPass a)
+static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *tile, const uint32_t vbx, const uint32_t nwarps)
 {
     constexpr int QA = 1 << A, QB = 1 << B, LOGQ = A + B;
-    GLP_DYN_SMEM(gl_t, tile);                                    // [Q][32] when B > 0
     const uint32_t lane = threadIdx.x % NTT_LANES, warp = threadIdx.x / NTT_LANES;
     const uint32_t ncg = (a.ncols + NTT_LANES - 1) / NTT_LANES;
     const uint64_t ntiles = 1ull << (a.logN - LOGQ);
-    const uint32_t cg = NARROW ? 0 : blockIdx.x % ncg;
-    uint64_t tix = NARROW ? blockIdx.x : blockIdx.x / ncg;
+    const uint32_t cg = NARROW ? 0 : vbx % ncg;
+    uint64_t tix = NARROW ? vbx : vbx / ncg;
     if (B == 0) tix = tix * NTT_WARPS + warp;
     if (NARROW) tix = (tix << (5 - a.log_cw)) + (lane >> a.log_cw);
     bool tileok = tix < ntiles;
@@ -247,7 +247,7 @@ k_ntt_pass(NttPass a)
 
     // ---- step 1: 2^A-point transforms over the high digit of q = m*QB + b ----
 #pragma unroll 1
-    for (uint32_t b = (B == 0 ? 0 : warp); b < (uint32_t)QB; b += NTT_WARPS) {
+    for (uint32_t b = (B == 0 ? 0 : warp); b < (uint32_t)QB; b += nwarps) {
         gl_t v[QA];
         {
             const uint64_t r0 = ((uint64_t)b << logS) + p;       // input row of m = 0 inside the sub-transform
@@ -289,13 +289,39 @@ k_ntt_pass(NttPass a)
 
     // ---- step 2: 2^B-point transforms over b; tile output t = u + QA*w ----
 #pragma unroll 1
-    for (uint32_t u = warp; u < (uint32_t)QA; u += NTT_WARPS) {
+    for (uint32_t u = warp; u < (uint32_t)QA; u += nwarps) {
         gl_t v[QB];
         const gl_t *trow = tile + (size_t)u * QB * NTT_LANES + lane;
 #pragma unroll
         for (int b = 0; b < QB; b++) v[b] = trow[(size_t)b * NTT_LANES];
         ntt_dft_regs<B, 0>(v);
         ntt_store_outputs<B, INV>(a, sl, v, u, QA, p, omul, fptr, fsh, fkind, fbase, fbsh, rbase, rsh, col, colok);
+    }
+}
+
+template <int A, int B, bool INV, int LSH, bool NARROW>
+__global__ void __launch_bounds__(NTT_THREADS, 2)
+k_ntt_pass(NttPass a)
+{
+    GLP_DYN_SMEM(gl_t, tile);                                    // [Q][32] when B > 0
+    ntt_pass_block<A, B, INV, LSH, NARROW>(a, tile, blockIdx.x, NTT_WARPS);
+}
+
+// Co-resident flavour (two-step tiles only): a grid of a few CTAs per SM, each of blockDim.x/32 <= 16 warps, walks
+// the `nvb` block indices of k_ntt_pass.  It is launched on a high-priority stream UNDER a running leaf-hash kernel
+// (commit_overlapped in capi.cu): its whole grid becomes resident as soon as hash CTAs retire, takes a fixed slice of
+// every SM (16 K registers and 64 KB of shared memory at 256 threads) and leaves the rest to the hash, so the LDE of
+// column block k+1 runs in the issue slots and ALU cycles that the multiplier-bound hash of block k leaves idle.
+template <int A, int B, bool INV, int LSH>
+__global__ void __launch_bounds__(NTT_THREADS, 2)
+k_ntt_pass_co(NttPass a, uint32_t nvb)
+{
+    static_assert(B > 0, "co-resident passes are two-step tiles");
+    GLP_DYN_SMEM(gl_t, tile);
+    const uint32_t nwarps = blockDim.x / NTT_LANES;
+    for (uint32_t vbx = blockIdx.x; vbx < nvb; vbx += gridDim.x) {
+        ntt_pass_block<A, B, INV, LSH, false>(a, tile, vbx, nwarps);
+        __syncthreads();                                         // the tile buffer is reused by the next block index
     }
 }
 

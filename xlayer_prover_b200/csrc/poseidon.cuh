@@ -82,6 +82,26 @@ GL_HD void gl_dot_mac(GlDotAcc &s, gl_t a, gl_t b)
 }
 
 #ifndef POS_EPS_ALU_FOLD
+#define POS_EPS_ALU_FOLD 0
+#endif
+#ifndef POS_EPS_ALU_MULADD
+#define POS_EPS_ALU_MULADD 0
+#endif
+#ifndef POS_RED_MODE
+#define POS_RED_MODE 0            // fold of the S-box multiplies: 0 IMAD.LO+IMAD.HI, 1 ALU, 2 one IMAD.WIDE (gl_reduce128_m)
+#endif
+#ifndef POS_MUL4W
+#define POS_MUL4W 0               // 1: S-box / rank-1 products as four IMAD.WIDE (gl_mul_wide4)
+#endif
+#ifndef POS_MULADD_MODE
+#define POS_MULADD_MODE (POS_EPS_ALU_MULADD ? 1 : 0)
+#endif
+#ifndef POS_FOLD_MODE
+#define POS_FOLD_MODE (POS_EPS_ALU_FOLD ? 1 : 0)
+#endif
+GL_HD gl_t pos_pow7(gl_t x) { return gl_pow7_m<POS_RED_MODE, POS_MUL4W != 0>(x); }
+
+#ifndef POS_EPS_ALU_FOLD
 #define POS_EPS_ALU_FOLD 0        // 1: the p2*EPS term of the dot-product folds on the ALU pipe (experiment)
 #endif
 #ifndef POS_EPS_ALU_MULADD
@@ -97,7 +117,7 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
     uint64_t l4 = (uint64_t)s.yc + (t3 >> 32);
     gl_t lo = ((t1 & 0xFFFFFFFFULL) << 32) | s.z0;
     gl_t hi = ((t3 & 0xFFFFFFFFULL) << 32) | (t2 & 0xFFFFFFFFULL);
-    gl_t r = gl_reduce128_t<POS_EPS_ALU_FOLD != 0>(lo, hi);
+    gl_t r = gl_reduce128_m<POS_FOLD_MODE>(lo, hi);
     return gl_sub(r, l4 << 32);
 }
 
@@ -105,7 +125,8 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
 GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c)
 {
     gl_t lo, hi;
-    gl_mul_wide(a, b, lo, hi);
+    if (POS_MUL4W) gl_mul_wide4(a, b, lo, hi);
+    else gl_mul_wide(a, b, lo, hi);
 #if GL_DEVICE_PTX
     asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(lo), "+l"(hi) : "l"(c));
 #else
@@ -113,7 +134,7 @@ GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c)
     hi += (t < lo);
     lo = t;
 #endif
-    return gl_reduce128_t<POS_EPS_ALU_MULADD != 0>(lo, hi);
+    return gl_reduce128_m<POS_MULADD_MODE>(lo, hi);
 }
 
 // ---- MDS layer: state' = M^T state,  M[j][i] = circ[(j-i) mod 12] (+8 at i=j=0) ----
@@ -308,19 +329,19 @@ GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc)
     static_assert(12 % G == 0, "POS_SBOX_GROUP must divide 12");
     if (!rc) {
 #pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = gl_pow7(x[i]);
+        for (int i = 0; i < 12; i++) x[i] = pos_pow7(x[i]);
         return;
     }
     if (G == 12) {
 #pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = gl_add_c(gl_pow7(x[i]), rc[i]);
+        for (int i = 0; i < 12; i++) x[i] = gl_add_c(pos_pow7(x[i]), rc[i]);
         return;
     }
 #pragma unroll 1
     for (int q = 0; q < 12 / G; q++) {
         gl_t t[G];
 #pragma unroll
-        for (int i = 0; i < G; i++) t[i] = gl_add_c(gl_pow7(x[i]), rc[q * G + i]);
+        for (int i = 0; i < G; i++) t[i] = gl_add_c(pos_pow7(x[i]), rc[q * G + i]);
 #pragma unroll
         for (int i = 0; i + G < 12; i++) x[i] = x[i + G];
 #pragma unroll
@@ -403,7 +424,7 @@ GL_HD void pos_permute_t(gl_t x[12])
             for (int p = 0; p < 22; p++) {
                 pos_round_sync<LOCKSTEP>();
                 const gl_t *S = POS_SP + 23 * p;
-                x[0] = gl_add_c(gl_pow7(x[0]), POS_RC[60 + p]);
+                x[0] = gl_add_c(pos_pow7(x[0]), POS_RC[60 + p]);
                 GlDotAcc acc;
                 gl_dot_init(acc);
 #pragma unroll
