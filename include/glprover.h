@@ -130,6 +130,19 @@ int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source
 int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
                uint64_t n, uint64_t n_ext, uint64_t ncols);
 
+/* ---- the callers either side of the commit ---- */
+/* Step 4 of Starks::genProof, the quotient commit (src/starkpil/starks.cpp:261-291):
+ *   qq1 = INTT_{n_ext}(q)  (q: n_ext x qdim);  qq2[k][p*qdim+d] = qq1[p*n+k][d] * shift^(-n*p)  (k < n, p < qdeg);
+ *   cm4 = NTT_{n_ext}(qq2 zero-padded)  (n_ext x qdim*qdeg);  tree = merkletree(cm4).
+ * cm4 / tree / root may be NULL (not wanted); host or device pointers. */
+int glp_quotient_commit(glp_ctx *ctx, uint64_t *cm4, uint64_t *tree, uint64_t root[4], const uint64_t *q, uint64_t n,
+                        uint64_t n_ext, uint64_t qdim, uint64_t qdeg);
+/* The constant tree as bctree writes it and MerkleTreeGL(Goldilocks::Element *tree) maps it
+ * (tools/starkpil/bctree/build_const_tree.cpp:555-575; src/starkpil/merkleTree/merkleTreeGL.hpp:24-32):
+ * const_tree = [npols, n_ext, extendPol(const_pols) (n_ext x npols), Merkle nodes]; the root is its last 4 words. */
+uint64_t glp_const_tree_num_elements(uint64_t n_ext, uint64_t npols);
+int glp_const_tree(glp_ctx *ctx, uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols);
+
 /* ---- synthetic data and checks used by bench.py / tests ---- */
 /* dst[i*ncols + c] = splitmix64(seed ^ ((row0+i)*ncols_total + col0 + c)) mod p, generated on the device */
 int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0,

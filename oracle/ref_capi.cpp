@@ -7,6 +7,9 @@
 //   NTT_Goldilocks      $REF/src/goldilocks/src/ntt_goldilocks.{hpp,cpp}
 //   PoseidonGoldilocks  $REF/src/goldilocks/src/poseidon_goldilocks.{hpp,cpp}
 //   MerkleTreeGL        $REF/src/starkpil/merkleTree/merkleTreeGL.{hpp,cpp}
+//   Transcript          $REF/src/starkpil/transcript/transcript.{hpp,cpp}
+// or, for the two call sequences that live inside Starks::genProof / bctree (which do not compile stand-alone),
+// repeats that sequence of reference calls with the line numbers it follows.
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -17,6 +20,8 @@
 #include "poseidon_goldilocks.hpp"
 #include "merklehash_goldilocks.hpp"
 #include "merkleTreeGL.hpp"
+#include "transcript.hpp"
+#include <vector>
 
 typedef Goldilocks::Element E;
 static_assert(sizeof(E) == sizeof(uint64_t), "Element must be a bare uint64_t");
@@ -153,4 +158,48 @@ int ref_commit(uint64_t *out_ext, uint64_t *tree, uint64_t *in, uint64_t n, uint
     if (seconds) { seconds[0] = t1 - t0; seconds[1] = t2 - t1; }
     return 0;
 }
+
+// ---- step 4 of Starks::genProof, the quotient commit (starks.cpp:232-233,261-291): INTT of the quotient on the
+// extended domain (qDim columns), split into qDeg chunks of N coefficients scaled by shiftIn^p, shiftIn = shift^-N
+// (:264-281; Goldilocks3::mul by a base-field scalar is a per-component multiply), forward NTT of the zero-padded
+// N x (qDeg*qDim) matrix (:285), Merkle tree over its NExtended rows (:290). ----
+int ref_quotient_commit(uint64_t *cm4, uint64_t *tree, uint64_t *q_2ns, uint64_t N, uint64_t NExtended, uint64_t qDim, uint64_t qDeg)
+{
+    NTT_Goldilocks nttExtended(NExtended);
+    std::vector<E> qq1(NExtended * qDim), qq2(NExtended * qDeg * qDim);
+    std::memset((void *)qq2.data(), 0, qq2.size() * sizeof(E));
+    nttExtended.INTT(qq1.data(), (E *)q_2ns, NExtended, qDim, NULL, 2, 1);
+    E shiftIn = Goldilocks::exp(Goldilocks::inv(Goldilocks::shift()), N);
+    E curS = Goldilocks::one();
+    for (uint64_t p = 0; p < qDeg; p++) {
+        for (uint64_t k = 0; k < N; k++)
+            for (uint64_t d = 0; d < qDim; d++) qq2[(k * qDeg + p) * qDim + d] = Goldilocks::mul(qq1[(p * N + k) * qDim + d], curS);
+        curS = Goldilocks::mul(curS, shiftIn);
+    }
+    nttExtended.NTT((E *)cm4, qq2.data(), NExtended, qDim * qDeg);
+    if (tree) PoseidonGoldilocks::merkletree((E *)tree, (E *)cm4, qDim * qDeg, NExtended);
+    return 0;
+}
+
+// ---- the constant tree as bctree lays it out (tools/starkpil/bctree/build_const_tree.cpp:531-575): header
+// [nPols, nExt], the extended constant polynomials, the Merkle nodes.  bctree's own `interpolate` (:398-470) is the
+// same map as NTT_Goldilocks::extendPol (INTT, * shift^i / N, zero-padded NTT), which is what is called here. ----
+int ref_const_tree(uint64_t *const_tree, uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols)
+{
+    NTT_Goldilocks ntt(n);
+    std::vector<E> buffer(n_ext * npols);
+    const_tree[0] = npols;
+    const_tree[1] = n_ext;
+    ntt.extendPol((E *)const_tree + 2, (E *)const_pols, n_ext, n, npols, buffer.data());
+    PoseidonGoldilocks::merkletree((E *)const_tree + 2 + npols * n_ext, (E *)const_tree + 2, npols, n_ext);
+    return 0;
+}
+
+// ---- Transcript (transcript.cpp:4-91) ----
+void *ref_tr_new(void) { return new Transcript(); }
+void ref_tr_free(void *t) { delete (Transcript *)t; }
+void ref_tr_put(void *t, uint64_t *in, uint64_t n) { ((Transcript *)t)->put((E *)in, n); }
+void ref_tr_get_field(void *t, uint64_t *out3) { ((Transcript *)t)->getField((E *)out3); }
+uint64_t ref_tr_get_fields1(void *t) { return Goldilocks::toU64(((Transcript *)t)->getFields1()); }
+void ref_tr_get_permutations(void *t, uint64_t *res, uint64_t n, uint64_t nbits) { ((Transcript *)t)->getPermutations(res, n, nbits); }
 } // extern "C"

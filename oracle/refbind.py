@@ -158,6 +158,53 @@ class RefLib(_Lib):
         L.ref_mt_get_root.restype, L.ref_mt_get_root.argtypes = None, [vp, u64p]
         L.ref_mt_get_group_proof.restype, L.ref_mt_get_group_proof.argtypes = None, [vp, u64p, u64]
 
+        L.ref_quotient_commit.restype, L.ref_quotient_commit.argtypes = C.c_int, [u64p, u64p, u64p, u64, u64, u64, u64]
+        L.ref_const_tree.restype, L.ref_const_tree.argtypes = C.c_int, [u64p, u64p, u64, u64, u64]
+        L.ref_tr_new.restype, L.ref_tr_new.argtypes = vp, []
+        L.ref_tr_free.restype, L.ref_tr_free.argtypes = None, [vp]
+        L.ref_tr_put.restype, L.ref_tr_put.argtypes = None, [vp, u64p, u64]
+        L.ref_tr_get_field.restype, L.ref_tr_get_field.argtypes = None, [vp, u64p]
+        L.ref_tr_get_fields1.restype, L.ref_tr_get_fields1.argtypes = u64, [vp]
+        L.ref_tr_get_permutations.restype, L.ref_tr_get_permutations.argtypes = None, [vp, u64p, u64, u64]
+
+    def quotient_commit(self, q, n, qdeg):
+        """Starks::genProof step 4 (starks.cpp:261-291) on q [n_ext x qdim]; returns (cm4, tree), canonical."""
+        q = np.ascontiguousarray(q, dtype=np.uint64)
+        n_ext, qdim = q.shape
+        cm4 = np.zeros((n_ext, qdim * qdeg), dtype=np.uint64)
+        tree = np.zeros(self._tree_num_elements(n_ext), dtype=np.uint64)
+        self.lib.ref_quotient_commit(_ptr(cm4), _ptr(tree), _ptr(q.copy()), n, n_ext, qdim, qdeg)
+        return self.canonical(cm4), self.canonical(tree)
+
+    def const_tree(self, const_pols, n_ext):
+        """bctree's *.consttree words [nPols, nExt, extended pols, nodes] (build_const_tree.cpp:555-575), canonical."""
+        a = np.ascontiguousarray(const_pols, dtype=np.uint64)
+        n, npols = a.shape
+        out = np.zeros(2 + npols * n_ext + self._tree_num_elements(n_ext), dtype=np.uint64)
+        self.lib.ref_const_tree(_ptr(out), _ptr(a.copy()), n, n_ext, npols)
+        return self.canonical(out)
+
+    def transcript(self):
+        """The reference's Transcript object behind a small Python face (put / get_field / get_fields1 / get_permutations)."""
+        L = self.lib
+
+        class _T:
+            def __init__(s): s.h = L.ref_tr_new()
+            def __del__(s): L.ref_tr_free(s.h)
+            def put(s, a):
+                a = np.ascontiguousarray(a, dtype=np.uint64).reshape(-1)
+                L.ref_tr_put(s.h, _ptr(a), a.size)
+            def get_fields1(s): return int(L.ref_tr_get_fields1(s.h))
+            def get_field(s):
+                o = np.zeros(3, dtype=np.uint64)
+                L.ref_tr_get_field(s.h, _ptr(o))
+                return [int(x) % P for x in o]
+            def get_permutations(s, n, nbits):
+                o = np.zeros(n, dtype=np.uint64)
+                L.ref_tr_get_permutations(s.h, _ptr(o), n, nbits)
+                return [int(x) for x in o]
+        return _T()
+
     def is_avx512(self): return bool(self.lib.ref_is_avx512())
     def root(self, max_size, domain_pow, idx): return self.lib.ref_root(max_size, domain_pow, idx)
 

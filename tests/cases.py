@@ -163,3 +163,55 @@ def check_commit(ctx, oracle, a, n_ext, **kw):
     check_equal(ext, want_ext, "commit ext %s" % (a.shape,))
     check_equal(tree, want_tree, "commit tree %s" % (a.shape,))
     check_equal(root, want_tree[-4:], "commit root")
+
+
+# ---- the callers either side of the commit; the oracle is the reference build ----
+def check_quotient_commit(ctx, reference, rng, shapes=((16, 2, 3, 2), (64, 4, 3, 2), (32, 8, 3, 4), (128, 2, 1, 2))):
+    """Starks::genProof step 4 (starks.cpp:261-291): (n, blowup, qDim, qDeg) -> cm4 and every Merkle node."""
+    for n, blow, qdim, qdeg in shapes:
+        n_ext = n * blow
+        q = edge_matrix(rng, n_ext, qdim)
+        want_cm4, want_tree = reference.quotient_commit(q, n, qdeg)
+        cm4 = np.zeros((n_ext, qdim * qdeg), dtype=np.uint64)
+        tree = np.zeros(tree_words(n_ext), dtype=np.uint64)
+        root = ctx.quotient_commit(cm4, tree, q, n, n_ext, qdim, qdeg)
+        check_equal(cm4, want_cm4, "cm4 %s" % ((n, blow, qdim, qdeg),))
+        check_equal(tree, want_tree, "quotient tree")
+        check_equal(root, want_tree[-4:], "quotient root")
+        # device pointers, root only
+        dq = ctx.to_device(q)
+        check_equal(ctx.quotient_commit(None, None, dq, n, n_ext, qdim, qdeg), want_tree[-4:], "quotient root (device q)")
+        ctx.device_free(dq)
+
+
+def check_const_tree(ctx, reference, rng, shapes=((16, 2, 5), (64, 4, 21), (8, 2, 1))):
+    """bctree's *.consttree words and MerkleTreeGL(tree) mapping them back (build_const_tree.cpp:555-575, merkleTreeGL.hpp:24-32)."""
+    from xlayer_prover_b200 import MerkleTreeGL, build_const_tree
+    for n, blow, npols in shapes:
+        a = edge_matrix(rng, n, npols)
+        want = reference.const_tree(a, n * blow)
+        got = build_const_tree(a, n.bit_length() - 1, (n * blow).bit_length() - 1, ctx=ctx)
+        check_equal(got, want, "consttree %s" % ((n, blow, npols),))
+        mt = MerkleTreeGL(tree=got, ctx=ctx)
+        assert (mt.width, mt.height) == (npols, n * blow)
+        root = np.zeros(4, dtype=np.uint64)
+        mt.getRoot(root)
+        check_equal(root, want[-4:], "constRoot")
+
+
+def check_transcript(ctx, reference, rng):
+    """Transcript put/getField/getPermutations against the reference class on the same call sequence (transcript.cpp:4-91)."""
+    from xlayer_prover_b200 import Transcript
+    ours, ref = Transcript(ctx=ctx), reference.transcript()
+    assert ours.getField() == ref.get_field()                      # squeeze from the empty state
+    for size in (4, 8, 3, 13, 1):                                   # a Merkle root, a full block, ragged pieces
+        a = rng.integers(0, P, size=size, dtype=np.uint64)
+        ours.put(a)
+        ref.put(a)
+        assert ours.getField() == ref.get_field(), "getField after put(%d)" % size
+    ours.put(np.array([P - 1, 0, 5], dtype=np.uint64))
+    ref.put(np.array([P - 1, 0, 5], dtype=np.uint64))
+    for _ in range(14):                                             # runs through all 12 outputs and re-permutes
+        assert ours.getFields1() == ref.get_fields1()
+    assert ours.getPermutations(64, 23) == ref.get_permutations(64, 23)   # nQueries x nBitsExt bits -> 24 field elements
+    assert ours.getPermutations(3, 5) == ref.get_permutations(3, 5)

@@ -4,6 +4,7 @@
 // libglprover.so; needs a GPU to run (there is no CPU path behind the classes).
 #include "merkleTreeGL.hpp"
 #include "ntt_goldilocks.hpp"
+#include "transcript.hpp"
 #include <cstdio>
 #include <vector>
 
@@ -160,12 +161,33 @@ static void test_merkletree()
     EXPECT_EQ(Goldilocks::toU64(root[0]), 0X918F7CD0C3E8701FULL);
 }
 
+static void test_transcript()
+{
+    // answers produced by the reference's own Transcript (oracle/_ref, transcript.cpp) for put(1..19); getField; getPermutations(8, 5)
+    Transcript t;
+    std::vector<El> in(19);
+    for (uint64_t i = 0; i < 19; i++)
+        in[i].fe = i + 1;
+    t.put(in.data(), 19);
+    El f[3];
+    t.getField(f);
+    EXPECT_EQ(Goldilocks::toU64(f[0]), 14077115803306752431ULL);
+    EXPECT_EQ(Goldilocks::toU64(f[1]), 4970989821272620831ULL);
+    EXPECT_EQ(Goldilocks::toU64(f[2]), 17413480707857030579ULL);
+    uint64_t perm[8];
+    const uint64_t want[8] = {25, 8, 5, 7, 29, 13, 27, 26};
+    t.getPermutations(perm, 8, 5);
+    for (int i = 0; i < 8; i++)
+        EXPECT_EQ(perm[i], want[i]);
+}
+
 int main()
 {
     test_errors_and_inert();
     test_extendpol_kat();
     test_ntt_roundtrip();
     test_merkletree();
+    test_transcript();
     if (failures)
     {
         printf("%d failure(s)\n", failures);

@@ -9,8 +9,8 @@ import subprocess
 import numpy as np
 import pytest
 
-from cases import (P, check_commit, check_equal, check_ntt, edge_matrix, fib_matrix, fib_vector, run_extend,
-                   run_merkletree, tree_words)
+from cases import (P, check_commit, check_const_tree, check_equal, check_ntt, check_quotient_commit, check_transcript,
+                   edge_matrix, fib_matrix, fib_vector, run_extend, run_merkletree, tree_words)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 EMU = os.path.join(HERE, "cuemu", "libglprover_emu.so")
@@ -246,6 +246,16 @@ def test_commit_overlapped(emu_lib, oracle, rng):
     check_commit(c, oracle, a, 256, device=True)
     assert c.launch_count() - launches0 >= 3 * 2 + 3      # one INTT + one NTT pass and one absorption per block, plus the levels
     c.close()
+
+
+def test_quotient_commit(ectx, ectx3, reference, rng):
+    check_quotient_commit(ectx, reference, rng)
+    check_quotient_commit(ectx3, reference, rng, shapes=((32, 2, 3, 2),))       # multi-pass transforms
+
+
+def test_const_tree_and_transcript(ectx, reference, rng):
+    check_const_tree(ectx, reference, rng)
+    check_transcript(ectx, reference, rng)
 
 
 def test_argument_errors(ectx):

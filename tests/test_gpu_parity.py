@@ -9,8 +9,9 @@ import os
 import numpy as np
 import pytest
 
-from cases import (P, check_commit, check_equal, check_ntt, edge_matrix, fib_matrix, fib_vector, monomial_columns,
-                   run_commit, run_extend, run_merkletree, run_ntt, tree_words)
+from cases import (P, check_commit, check_const_tree, check_equal, check_ntt, check_quotient_commit, check_transcript,
+                   edge_matrix, fib_matrix, fib_vector, monomial_columns, run_commit, run_extend, run_merkletree, run_ntt,
+                   tree_words)
 
 pytestmark = pytest.mark.gpu
 
@@ -491,3 +492,26 @@ def test_narrow_equals_wide_mapping(ctx, rng):
             check_equal(run_extend(ctx, a, 4 * n), run_extend(wide, a, 4 * n), "narrow vs wide extend %s" % ((n, c),))
     finally:
         wide.close()
+
+
+# ---------------------------------------------------------------- the callers either side of the commit
+def test_quotient_commit(ctx, reference, rng):
+    """Starks::genProof step 4 (starks.cpp:261-291) at test sizes and at a zkEVM-like shape (qDim 3, qDeg 2, blowup 2)"""
+    check_quotient_commit(ctx, reference, rng)
+    check_quotient_commit(ctx, reference, rng, shapes=((1 << 16, 2, 3, 2), (1 << 13, 8, 3, 4)))
+
+
+def test_const_tree_and_transcript(ctx, reference, rng):
+    check_const_tree(ctx, reference, rng)
+    check_const_tree(ctx, reference, rng, shapes=((1 << 12, 2, 44),))
+    check_transcript(ctx, reference, rng)
+
+
+def test_overlapped_commit_knob(oracle, rng):
+    """GLP_CO=1: LDE of column block k+1 (k_ntt_pass_co) under the leaf hash of block k -- off by default (slower,
+    profiles/r01_overlap_experiment.txt) but it must give the same bits.  2^14 rows so that the tiles are two-step."""
+    c = env_ctx(GLP_CO=1, GLP_CO_COLS=64, GLP_CO_FIRST=32)
+    try:
+        check_commit(c, oracle, edge_matrix(rng, 1 << 14, 200), 1 << 15, device=True)
+    finally:
+        c.close()

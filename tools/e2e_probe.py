@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """e2e (host-pointer) commit at the bench shape for several pipeline block widths; prints ms per commit and,
-with GLP_TRACE=1, the pipeline timeline.  usage: e2e_probe.py [log_rows] [cols] width [width ...]"""
+with GLP_TRACE=1, the pipeline timeline.  usage: e2e_probe.py [log_rows] [cols] width [width ...]
+E2E_MODE=full (default: extension + tree to the host) | root (no download at all) | tree (tree only)"""
 import ctypes
 import os
 import sys
@@ -29,7 +30,8 @@ for w in widths:
     roots = []
     for it in range(3):
         t0 = time.perf_counter()
-        roots.append(c.commit(hext, htree, hin, n, n_ext, C))
+        mode = os.environ.get("E2E_MODE", "full")
+        roots.append(c.commit(hext if mode == "full" else None, None if mode == "root" else htree, hin, n, n_ext, C))
         dt = time.perf_counter() - t0
         print("width %4d  iter %d  %8.1f ms  root[0] %#x" % (w, it, dt * 1e3, int(roots[-1][0])), flush=True)
     c.close()

@@ -177,3 +177,89 @@ class MerkleTreeGL:
         """merkleTreeGL.cpp:12-35: row idx, then the sibling path."""
         self.ctx.merkle_group_proof(proof, self.source, self.nodes, self.width, self.height, idx)
         return proof
+
+
+class Transcript:
+    """Fiat-Shamir transcript of the STARK (src/starkpil/transcript/transcript.{hpp,cpp}): a Poseidon sponge that
+    absorbs 8 words at a time (`pending`), keeps 4 words of `state`, and hands out the 12 outputs of the last
+    permutation in order.  Same members and methods as the reference class; every permutation is one
+    glp_hash_full_result call on the GPU (the host keeps only the cursors)."""
+
+    STATE_SIZE, PENDING_SIZE, OUT_SIZE = 4, 8, 12          # transcript.hpp:8-10
+
+    def __init__(self, ctx=None):
+        self._ctx = ctx
+        self.state = np.zeros(self.STATE_SIZE, dtype=np.uint64)
+        self.pending = np.zeros(self.PENDING_SIZE, dtype=np.uint64)
+        self.out = np.zeros(self.OUT_SIZE, dtype=np.uint64)
+        self.pending_cursor = 0
+        self.out_cursor = 0
+        self.state_cursor = 0
+
+    @property
+    def ctx(self):
+        return self._ctx or default_context()
+
+    def _permute(self):
+        """transcript.cpp:19-29 / :45-55: out = hash_full_result(pending || state); state = out[0:4]; pending cleared"""
+        inputs = np.concatenate([self.pending, self.state])
+        self.ctx.hash_full_result(self.out, inputs, 1)
+        self.out_cursor = self.OUT_SIZE
+        self.pending[:] = 0
+        self.pending_cursor = 0
+        self.state[:] = self.out[:self.STATE_SIZE]
+
+    def _add1(self, value):
+        self.pending[self.pending_cursor] = value
+        self.pending_cursor += 1
+        self.out_cursor = 0
+        if self.pending_cursor == self.PENDING_SIZE:
+            self._permute()
+
+    def put(self, input, size=None):
+        a = np.asarray(input, dtype=np.uint64).reshape(-1)
+        for v in a[: a.size if size is None else size]:
+            self._add1(v)
+
+    def getFields1(self):
+        if self.out_cursor == 0:
+            self._permute()
+        res = self.out[(self.OUT_SIZE - self.out_cursor) % self.OUT_SIZE]
+        self.out_cursor -= 1
+        return int(res)
+
+    def getField(self, output=None):
+        vals = [self.getFields1() for _ in range(3)]
+        if output is not None:
+            output[:3] = vals
+        return vals
+
+    def getPermutations(self, n, nBits):
+        """transcript.cpp:58-91: n indices of nBits bits cut from the low 63 bits of successive field elements"""
+        total_bits = n * nBits
+        nfields = (total_bits - 1) // 63 + 1
+        fields = [self.getFields1() for _ in range(nfields)]
+        res, cur_field, cur_bit = [], 0, 0
+        for _ in range(n):
+            a = 0
+            for j in range(nBits):
+                if (fields[cur_field] >> cur_bit) & 1:
+                    a += 1 << j
+                cur_bit += 1
+                if cur_bit == 63:
+                    cur_bit, cur_field = 0, cur_field + 1
+            res.append(a)
+        return res
+
+
+def build_const_tree(const_pols, nBits, nBitsExt, ctx=None):
+    """bctree's buildConstTree for verificationHashType GL (tools/starkpil/bctree/build_const_tree.cpp:531-575):
+    returns the *.consttree words [nPols, nExt, extended constant polynomials, Merkle nodes]; the constRoot of
+    verkey.json is its last four words.  MerkleTreeGL(tree=...) maps it back (merkleTreeGL.hpp:24-32)."""
+    ctx = ctx or default_context()
+    a = np.ascontiguousarray(const_pols, dtype=np.uint64)
+    n, n_ext = 1 << nBits, 1 << nBitsExt
+    npols = a.size // n
+    out = np.zeros(2 + npols * n_ext + tree_num_elements(n_ext), dtype=np.uint64)
+    ctx.const_tree(out, a, n, n_ext, npols)
+    return out

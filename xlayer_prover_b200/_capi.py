@@ -51,6 +51,9 @@ SIGNATURES = {
     "glp_tree_num_elements": (u64, [u64]),
     "glp_merkle_group_proof": (i32, [vp, vp, vp, vp, u64, u64, u64]),
     "glp_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64]),
+    "glp_quotient_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64, u64]),
+    "glp_const_tree_num_elements": (u64, [u64, u64]),
+    "glp_const_tree": (i32, [vp, vp, vp, u64, u64, u64]),
     "glp_synth_fill": (i32, [vp, vp, u64, u64, u64, u64, u64, u64]),
     "glp_checksum": (i32, [vp, vp, u64, u64p]),
     "glp_field_selftest": (i32, [vp, vp, vp, u64, vp]),
@@ -229,6 +232,16 @@ class Context:
         root = np.zeros(4, dtype=np.uint64)
         self.lib.check(self.lib.glp_commit(self.h, ptr_of(out_ext), ptr_of(tree), ptr_of(root), ptr_of(inp), n, n_ext, ncols))
         return root
+
+    def quotient_commit(self, cm4, tree, q, n, n_ext, qdim, qdeg):
+        """Starks::genProof step 4 (starks.cpp:261-291): cm4 = NTT(split(INTT(q))), tree over cm4; returns the root."""
+        root = np.zeros(4, dtype=np.uint64)
+        self.lib.check(self.lib.glp_quotient_commit(self.h, ptr_of(cm4), ptr_of(tree), ptr_of(root), ptr_of(q), n, n_ext, qdim, qdeg))
+        return root
+
+    def const_tree(self, const_tree, const_pols, n, n_ext, npols):
+        """bctree's *.consttree layout [npols, n_ext, extended pols, nodes] (build_const_tree.cpp:555-575)."""
+        self.lib.check(self.lib.glp_const_tree(self.h, ptr_of(const_tree), ptr_of(const_pols), n, n_ext, npols))
 
     def synth_fill(self, dst, nrows, ncols, seed, row0=0, col0=0, ncols_total=None):
         self.lib.check(self.lib.glp_synth_fill(self.h, ptr_of(dst), nrows, ncols, row0, col0,

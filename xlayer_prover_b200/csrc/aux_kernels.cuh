@@ -67,6 +67,20 @@ __global__ void k_group_proof(gl_t *proof, const gl_t *source, const gl_t *nodes
     }
 }
 
+// Step 4 of Starks::genProof (src/starkpil/starks.cpp:264-281): the quotient's coefficients qq1 [qdeg*n x qdim] are cut
+// into qdeg chunks of n and chunk p, scaled by shift_in^p (shift_in = shift^-n), becomes columns [p*qdim, (p+1)*qdim) of
+// the n-row matrix qq2:  qq2[k][p*qdim + d] = qq1[p*n + k][d] * shift_in^p.
+__global__ void k_quotient_split(gl_t *qq2, const gl_t *qq1, uint64_t n, uint32_t qdim, uint32_t qdeg, gl_t shift_in)
+{
+    const uint64_t w = (uint64_t)qdim * qdeg, total = n * w;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t k = i / w, r = i % w, p = r / qdim, d = r % qdim;
+        gl_t s = 1;
+        for (uint64_t j = 0; j < p; j++) s = gl_mul(s, shift_in);
+        qq2[i] = gl_canon(gl_mul(qq1[(p * n + k) * qdim + d], s));
+    }
+}
+
 // NTT_Goldilocks::reversePermutation (ntt_goldilocks.cpp:243-305), out of place
 __global__ void k_reverse_permutation(gl_t *dst, const gl_t *src, uint64_t size, uint32_t logn, uint64_t offset_cols, uint64_t ncols,
                                       uint64_t ncols_all, uint64_t live)

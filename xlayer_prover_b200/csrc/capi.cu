@@ -60,6 +60,7 @@ struct glp_ctx {
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
+    bool stage_all = true;                   // GLP_STAGE_ALL=0: two alternating upload buffers even when the whole input fits
     bool no_narrow = false;                  // GLP_NTT_NO_NARROW=1: lane = column even for matrices of <= 16 columns (comparison runs)
     bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
     std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
@@ -175,6 +176,8 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_narrow = nn && atoi(nn) != 0;
     const char *tr = getenv("GLP_TRACE");
     ctx->trace = tr && atoi(tr) != 0;
+    const char *sa = getenv("GLP_STAGE_ALL");
+    if (sa) ctx->stage_all = atoi(sa) != 0;
     const char *sc = getenv("GLP_STREAM_COLS");
     if (sc && atoi(sc) >= 8) ctx->stream_cols = (uint64_t)(atoi(sc) / 8) * 8;
     *out = ctx;
@@ -1132,6 +1135,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
     // block width: GLP_STREAM_COLS (default 96), shrunk to fit the scratch budget
     uint64_t w = ctx->stream_cols;
+    bool full_stage = false;
     {
         size_t f = 0, t = 0;
         if (cudaMemGetInfo(&f, &t) != cudaSuccess) { cudaGetLastError(); f = (size_t)1 << 30; }
@@ -1140,6 +1144,10 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         if (ctx->scratch_limit && ctx->scratch_limit < budget) budget = ctx->scratch_limit;
         const uint64_t per_col = 8 * (2 * n + (ext_dev ? 0 : 2 * n_ext) + n);
         while (w > 8 && w * per_col > budget) w -= 8;
+        // When the whole input also fits, every block gets its own staging slice and the upload runs ahead at full
+        // rate instead of in step with the LDE: the download -- the longest stream of the pipeline -- then shares the
+        // PCIe link with an upload for the first 0.85 s only (2-D downloads: 43 GB/s next to an upload, 47 GB/s alone).
+        full_stage = ctx->stage_all && 8 * n * (ncols + 8) + (w + 8) * (per_col - 16 * n) <= budget;
     }
     // Blocks in units of 8 columns.  The first block is short (32 columns) so that the GPU starts after a short
     // upload -- nothing overlaps the first upload; the rest are equal (a short LAST block would only be copied in
@@ -1163,9 +1171,9 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         col0[k + 1] = c1 < ncols ? c1 : ncols;
     }
     col0[nblocks] = ncols;
-    GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * w * sizeof(gl_t)));
+    GLP(ensure(ctx, ctx->tmp_in, (full_stage ? (size_t)n * (col0[nblocks] + 8) : 2 * (size_t)n * w) * sizeof(gl_t)));
     if (!ext_dev) GLP(ensure(ctx, ctx->tmp_out, 2 * (size_t)n_ext * w * sizeof(gl_t)));
-    gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
+    auto stage_of = [&](uint64_t k) { return (gl_t *)ctx->tmp_in.p + (full_stage ? (size_t)n * col0[k] : (k & 1) * (size_t)n * w); };
     gl_t *extb[2] = {(gl_t *)ctx->tmp_out.p, ext_dev ? nullptr : (gl_t *)ctx->tmp_out.p + (size_t)n_ext * w};
     std::vector<cudaEvent_t> up(nblocks), lde_done(nblocks), down(nblocks), hashed(nblocks);
     const unsigned evflags = ctx->trace ? cudaEventDefault : cudaEventDisableTiming;     // GLP_TRACE=1: print the pipeline's timeline
@@ -1182,14 +1190,16 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     CU(cudaStreamWaitEvent(ctx->copy_stream[1], start, 0));
     auto width = [&](uint64_t k) { return (uint32_t)(col0[k + 1] - col0[k]); };
     auto upload = [&](uint64_t k) -> int {
-        if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
-        CU(cudaMemcpy2DAsync(stage[k & 1], (size_t)width(k) * 8, in + col0[k], (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
+        if (k >= 2 && !full_stage) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
+        CU(cudaMemcpy2DAsync(stage_of(k), (size_t)width(k) * 8, in + col0[k], (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
                              ctx->copy_stream[0]));
         CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
         return GLP_OK;
     };
     GLP(upload(0));
     if (nblocks > 1) GLP(upload(1));
+    if (full_stage)
+        for (uint64_t k = 2; k < nblocks; k++) GLP(upload(k));
     for (uint64_t k = 0; k < nblocks; k++) {
         const uint64_t c0 = col0[k];
         const uint32_t wk = width(k);
@@ -1197,9 +1207,9 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         const uint64_t eb_pitch = ext_dev ? ncols : wk;
         CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
         if (!ext_dev && want_ext && k >= 2) CU(cudaStreamWaitEvent(ctx->stream, down[k - 2], 0));   // extension buffer still being downloaded
-        GLP(lde_block(ctx, logN, logE, stage[k & 1], wk, eb, eb_pitch, wk));
+        GLP(lde_block(ctx, logN, logE, stage_of(k), wk, eb, eb_pitch, wk));
         CU(cudaEventRecord(lde_done[k], ctx->stream));
-        if (k + 2 < nblocks) GLP(upload(k + 2));
+        if (k + 2 < nblocks && !full_stage) GLP(upload(k + 2));
         if (want_ext && !ext_dev) {
             CU(cudaStreamWaitEvent(ctx->copy_stream[1], lde_done[k], 0));
             CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)ncols * 8, eb, (size_t)wk * 8, (size_t)wk * 8, n_ext, cudaMemcpyDeviceToHost,
@@ -1340,6 +1350,76 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
     if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return GLP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// the callers either side of the commit
+// ------------------------------------------------------------------------------------------------
+// Step 4 of Starks::genProof (src/starkpil/starks.cpp:261-291): INTT of the quotient over the extended domain (qdim
+// columns), chunk p of n coefficients scaled by shift^(-n p) into columns [p*qdim, (p+1)*qdim) (k_quotient_split),
+// forward NTT of that n-row matrix zero-padded to n_ext rows, Merkle tree over the n_ext rows of the result.
+// Everything between the input and cm4/tree stays on the device; narrow matrices (3 -> 6 columns) take the NARROW
+// lane mapping of k_ntt_pass.
+extern "C" int glp_quotient_commit(glp_ctx *ctx, uint64_t *cm4, uint64_t *tree, uint64_t root[4], const uint64_t *q, uint64_t n,
+                                   uint64_t n_ext, uint64_t qdim, uint64_t qdeg)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (n == 0 || qdim == 0 || qdeg == 0) return GLP_OK;
+    if (!q) return fail(GLP_E_ARG, "glp_quotient_commit: q is NULL");
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n || qdeg * n > n_ext)
+        return fail(GLP_E_ARG, "glp_quotient_commit: sizes must be powers of two with qdeg * n <= n_ext");
+    if (n_ext > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    if (qdim * qdeg > 0xFFFFu) return fail(GLP_E_ARG, "glp_quotient_commit: too many columns");
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t logE = ilog2_u64(n_ext);
+    const uint64_t w = qdim * qdeg;
+    const size_t tree_words = glp_tree_num_elements(n_ext);
+    const bool want_tree = tree != nullptr || root != nullptr;
+    const bool cm_dev = on_device(cm4), tree_dev = on_device(tree);
+    const gl_t *dq = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, q, (size_t)n_ext * qdim, &dq));
+    GLP(ensure(ctx, ctx->work, ((size_t)n_ext * qdim + (size_t)n * w) * sizeof(gl_t)));
+    gl_t *qq1 = (gl_t *)ctx->work.p, *qq2 = qq1 + (size_t)n_ext * qdim;
+    GLP(ensure(ctx, ctx->s1, (size_t)n_ext * w * sizeof(gl_t)));
+    gl_t *dcm = (gl_t *)cm4;
+    if (!cm_dev) { GLP(ensure(ctx, ctx->ext, (size_t)n_ext * w * sizeof(gl_t))); dcm = (gl_t *)ctx->ext.p; }
+    gl_t *dtree = (gl_t *)tree;
+    if (want_tree && !tree_dev) { GLP(ensure(ctx, ctx->nodes, tree_words * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+    {
+        ProfScope ps(ctx, 0);
+        GLP(run_transform(ctx, logE, dq, qdim, qq1, qdim, (uint32_t)qdim, n_ext, true, false, (gl_t *)ctx->s1.p));
+        const gl_t shift_in = gl_canon(gl_pow(gl_inv((gl_t)GL_SHIFT), n));
+        const uint64_t nb = (n * w + 255) / 256;
+        LAUNCH_FLAT(ctx, k_quotient_split, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, qq2, (const gl_t *)qq1, n, (uint32_t)qdim, (uint32_t)qdeg, shift_in);
+        CU(cudaGetLastError());
+    }
+    {
+        ProfScope ps(ctx, 1);
+        GLP(run_transform(ctx, logE, qq2, w, dcm, w, (uint32_t)w, n, false, false, (gl_t *)ctx->s1.p));
+    }
+    if (cm4 && !cm_dev) CU(cudaMemcpyAsync(cm4, dcm, (size_t)n_ext * w * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (want_tree) GLP(dev_merkletree(ctx, dtree, dcm, w, w, n_ext));
+    if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+// The constant tree in the layout bctree writes and MerkleTreeGL(Goldilocks::Element *tree) maps
+// (tools/starkpil/bctree/build_const_tree.cpp:555-575; merkleTreeGL.hpp:24-32):
+//     [npols, n_ext, extended constant polynomials (n_ext x npols), Merkle nodes ((2 n_ext - 1) x 4)]
+// bctree's `interpolate` (:398-470) is the same map as extendPol, so this is glp_commit writing into one buffer.
+extern "C" uint64_t glp_const_tree_num_elements(uint64_t n_ext, uint64_t npols) { return 2 + npols * n_ext + glp_tree_num_elements(n_ext); }
+extern "C" int glp_const_tree(glp_ctx *ctx, uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!const_tree || !const_pols) return fail(GLP_E_ARG, "glp_const_tree: NULL pointer");
+    if (n == 0 || npols == 0) return fail(GLP_E_ARG, "glp_const_tree: empty input");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t header[2] = {npols, n_ext};
+    CU(cudaMemcpyAsync(const_tree, header, sizeof header, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));                       // `header` is a stack buffer
+    return glp_commit(ctx, const_tree + 2, const_tree + 2 + npols * n_ext, nullptr, const_pols, n, n_ext, npols);
 }
 
 // ------------------------------------------------------------------------------------------------
