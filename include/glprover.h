@@ -143,6 +143,17 @@ int glp_quotient_commit(glp_ctx *ctx, uint64_t *cm4, uint64_t *tree, uint64_t ro
 uint64_t glp_const_tree_num_elements(uint64_t n_ext, uint64_t npols);
 int glp_const_tree(glp_ctx *ctx, uint64_t *const_tree, const uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols);
 
+/* ---- FRI layers on the device ---- */
+/* One folding step of FRIProve::prove (src/starkpil/fri/friProve.cpp:22-108, si > 0): pol holds 2^pol_bits elements of
+ * the cubic extension (3 words each); out[g] = evalPol(polMulAxi(INTT_{nX}(pol[i*2^step_bits + g]), shift_inv * w^-g), special_x),
+ * g < 2^step_bits, nX = 2^(pol_bits - step_bits) <= 64. */
+int glp_fri_fold(glp_ctx *ctx, uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint32_t step_bits, const uint64_t special_x[3],
+                 uint64_t shift_inv);
+/* The layer's tree (friProve.cpp:110-123, getTransposed :252-270): aux = pol regrouped into 2^next_bits rows,
+ * tree = MerkleTreeGL(2^next_bits, 3 * 2^(pol_bits - next_bits), aux).  aux / tree / root may be NULL. */
+int glp_fri_group_tree(glp_ctx *ctx, uint64_t *aux, uint64_t *tree, uint64_t root[4], const uint64_t *pol, uint32_t pol_bits,
+                       uint32_t next_bits);
+
 /* ---- synthetic data and checks used by bench.py / tests ---- */
 /* dst[i*ncols + c] = splitmix64(seed ^ ((row0+i)*ncols_total + col0 + c)) mod p, generated on the device */
 int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0,

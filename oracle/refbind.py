@@ -160,6 +160,8 @@ class RefLib(_Lib):
 
         L.ref_quotient_commit.restype, L.ref_quotient_commit.argtypes = C.c_int, [u64p, u64p, u64p, u64, u64, u64, u64]
         L.ref_const_tree.restype, L.ref_const_tree.argtypes = C.c_int, [u64p, u64p, u64, u64, u64]
+        L.ref_fri_fold.restype, L.ref_fri_fold.argtypes = C.c_int, [u64p, u64p, u64, u64, u64p, u64]
+        L.ref_fri_group_tree.restype, L.ref_fri_group_tree.argtypes = C.c_int, [u64p, u64p, u64p, u64, u64]
         L.ref_tr_new.restype, L.ref_tr_new.argtypes = vp, []
         L.ref_tr_free.restype, L.ref_tr_free.argtypes = None, [vp]
         L.ref_tr_put.restype, L.ref_tr_put.argtypes = None, [vp, u64p, u64]
@@ -183,6 +185,23 @@ class RefLib(_Lib):
         out = np.zeros(2 + npols * n_ext + self._tree_num_elements(n_ext), dtype=np.uint64)
         self.lib.ref_const_tree(_ptr(out), _ptr(a.copy()), n, n_ext, npols)
         return self.canonical(out)
+
+    def fri_fold(self, pol, pol_bits, step_bits, special_x, shift_inv):
+        """one folding step of FRIProve::prove (friProve.cpp:22-108); pol [2^pol_bits x 3] -> [2^step_bits x 3], canonical"""
+        pol = np.ascontiguousarray(pol, dtype=np.uint64)
+        out = np.zeros((1 << step_bits, 3), dtype=np.uint64)
+        x = np.ascontiguousarray(special_x, dtype=np.uint64)
+        self.lib.ref_fri_fold(_ptr(out), _ptr(pol.copy()), pol_bits, step_bits, _ptr(x), int(shift_inv))
+        return self.canonical(out)
+
+    def fri_group_tree(self, pol, next_bits):
+        """getTransposed + MerkleTreeGL of a FRI layer (friProve.cpp:110-123,252-270); returns (aux, tree), canonical"""
+        pol = np.ascontiguousarray(pol, dtype=np.uint64)
+        n = pol.shape[0]
+        aux = np.zeros((1 << next_bits, 3 * (n >> next_bits)), dtype=np.uint64)
+        tree = np.zeros(self._tree_num_elements(1 << next_bits), dtype=np.uint64)
+        self.lib.ref_fri_group_tree(_ptr(aux), _ptr(tree), _ptr(pol.copy()), n, next_bits)
+        return self.canonical(aux), self.canonical(tree)
 
     def transcript(self):
         """The reference's Transcript object behind a small Python face (put / get_field / get_fields1 / get_permutations)."""

@@ -215,3 +215,29 @@ def check_transcript(ctx, reference, rng):
         assert ours.getFields1() == ref.get_fields1()
     assert ours.getPermutations(64, 23) == ref.get_permutations(64, 23)   # nQueries x nBitsExt bits -> 24 field elements
     assert ours.getPermutations(3, 5) == ref.get_permutations(3, 5)
+
+
+def check_fri_layers(ctx, reference, rng, pol_bits=10, steps=(7, 4, 2)):
+    """FRIProve::prove's step loop (friProve.cpp:20-148) for si > 0: fold 2^pol_bits -> 2^steps[0] -> ... with the coset shift
+    squared reduction_bits times per layer (:143-147), and every layer's regrouped Merkle tree (:110-123)."""
+    pol = edge_matrix(rng, 1 << pol_bits, 3)
+    shift_inv = pow(7, P - 2, P)
+    bits = pol_bits
+    for si, nb in enumerate(steps):
+        x = rng.integers(0, P, size=3, dtype=np.uint64)
+        want = reference.fri_fold(pol, bits, nb, x, shift_inv)
+        got = np.zeros((1 << nb, 3), dtype=np.uint64)
+        ctx.fri_fold(got, pol, bits, nb, x, shift_inv)
+        check_equal(got, want, "fri fold 2^%d -> 2^%d" % (bits, nb))
+        if si + 1 < len(steps):
+            nxt = steps[si + 1]
+            want_aux, want_tree = reference.fri_group_tree(want, nxt)
+            aux = np.zeros_like(want_aux)
+            tree = np.zeros(tree_words(1 << nxt), dtype=np.uint64)
+            root = ctx.fri_group_tree(aux, tree, got, nb, nxt)
+            check_equal(aux, want_aux, "fri layer source")
+            check_equal(tree, want_tree, "fri layer tree")
+            check_equal(root, want_tree[-4:], "fri layer root")
+        for _ in range(bits - nb):
+            shift_inv = shift_inv * shift_inv % P
+        pol, bits = want, nb

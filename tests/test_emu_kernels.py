@@ -9,7 +9,7 @@ import subprocess
 import numpy as np
 import pytest
 
-from cases import (P, check_commit, check_const_tree, check_equal, check_ntt, check_quotient_commit, check_transcript,
+from cases import (P, check_commit, check_const_tree, check_equal, check_fri_layers, check_ntt, check_quotient_commit, check_transcript,
                    edge_matrix, fib_matrix, fib_vector, run_extend, run_merkletree, tree_words)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -256,6 +256,11 @@ def test_quotient_commit(ectx, ectx3, reference, rng):
 def test_const_tree_and_transcript(ectx, reference, rng):
     check_const_tree(ectx, reference, rng)
     check_transcript(ectx, reference, rng)
+
+
+def test_fri_layers(ectx, reference, rng):
+    check_fri_layers(ectx, reference, rng)
+    check_fri_layers(ectx, reference, rng, pol_bits=7, steps=(1, 0))            # folds by 2^6 and 2^1, down to a constant
 
 
 def test_argument_errors(ectx):

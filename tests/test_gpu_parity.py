@@ -9,7 +9,8 @@ import os
 import numpy as np
 import pytest
 
-from cases import (P, check_commit, check_const_tree, check_equal, check_ntt, check_quotient_commit, check_transcript,
+from cases import (P, check_commit, check_const_tree, check_equal, check_fri_layers, check_ntt, check_quotient_commit,
+                   check_transcript,
                    edge_matrix, fib_matrix, fib_vector, monomial_columns, run_commit, run_extend, run_merkletree, run_ntt,
                    tree_words)
 
@@ -505,6 +506,13 @@ def test_const_tree_and_transcript(ctx, reference, rng):
     check_const_tree(ctx, reference, rng)
     check_const_tree(ctx, reference, rng, shapes=((1 << 12, 2, 44),))
     check_transcript(ctx, reference, rng)
+
+
+def test_fri_layers(ctx, reference, rng):
+    """FRI folding + layer trees at test sizes and at a recursive-prover-like schedule (2^20 -> 2^15 -> 2^10 -> 2^5)"""
+    check_fri_layers(ctx, reference, rng)
+    check_fri_layers(ctx, reference, rng, pol_bits=7, steps=(1, 0))
+    check_fri_layers(ctx, reference, rng, pol_bits=20, steps=(15, 10, 5))
 
 
 def test_overlapped_commit_knob(oracle, rng):

@@ -54,6 +54,8 @@ SIGNATURES = {
     "glp_quotient_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64, u64]),
     "glp_const_tree_num_elements": (u64, [u64, u64]),
     "glp_const_tree": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_fri_fold": (i32, [vp, vp, vp, u32, u32, vp, u64]),
+    "glp_fri_group_tree": (i32, [vp, vp, vp, vp, vp, u32, u32]),
     "glp_synth_fill": (i32, [vp, vp, u64, u64, u64, u64, u64, u64]),
     "glp_checksum": (i32, [vp, vp, u64, u64p]),
     "glp_field_selftest": (i32, [vp, vp, vp, u64, vp]),
@@ -242,6 +244,17 @@ class Context:
     def const_tree(self, const_tree, const_pols, n, n_ext, npols):
         """bctree's *.consttree layout [npols, n_ext, extended pols, nodes] (build_const_tree.cpp:555-575)."""
         self.lib.check(self.lib.glp_const_tree(self.h, ptr_of(const_tree), ptr_of(const_pols), n, n_ext, npols))
+
+    def fri_fold(self, out, pol, pol_bits, step_bits, special_x, shift_inv):
+        """one folding step of FRIProve::prove (friProve.cpp:22-108): 2^pol_bits -> 2^step_bits extension elements"""
+        x = (u64 * 3)(*[int(v) for v in special_x])
+        self.lib.check(self.lib.glp_fri_fold(self.h, ptr_of(out), ptr_of(pol), pol_bits, step_bits, x, int(shift_inv)))
+
+    def fri_group_tree(self, aux, tree, pol, pol_bits, next_bits):
+        """getTransposed + MerkleTreeGL of a FRI layer (friProve.cpp:110-123); returns the root"""
+        root = np.zeros(4, dtype=np.uint64)
+        self.lib.check(self.lib.glp_fri_group_tree(self.h, ptr_of(aux), ptr_of(tree), ptr_of(root), ptr_of(pol), pol_bits, next_bits))
+        return root
 
     def synth_fill(self, dst, nrows, ncols, seed, row0=0, col0=0, ncols_total=None):
         self.lib.check(self.lib.glp_synth_fill(self.h, ptr_of(dst), nrows, ncols, row0, col0,

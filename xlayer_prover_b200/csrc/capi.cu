@@ -6,6 +6,7 @@
 #include "poseidon_kernels.cuh"
 #include "ntt_kernels.cuh"
 #include "aux_kernels.cuh"
+#include "fri_kernels.cuh"
 
 #include <stdio.h>
 #include <stdlib.h>
@@ -1420,6 +1421,71 @@ extern "C" int glp_const_tree(glp_ctx *ctx, uint64_t *const_tree, const uint64_t
     CU(cudaMemcpyAsync(const_tree, header, sizeof header, cudaMemcpyDefault, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));                       // `header` is a stack buffer
     return glp_commit(ctx, const_tree + 2, const_tree + 2 + npols * n_ext, nullptr, const_pols, n, n_ext, npols);
+}
+
+// One FRI folding step (FRIProve::prove, src/starkpil/fri/friProve.cpp:22-108, the si > 0 branch): pol (2^pol_bits
+// extension elements, three words each) -> out (2^step_bits elements).  shift_inv is the inverse coset shift of THIS
+// layer (the reference squares it reduction_bits times after every step, :143-147).
+extern "C" int glp_fri_fold(glp_ctx *ctx, uint64_t *out, const uint64_t *pol, uint32_t pol_bits, uint32_t step_bits, const uint64_t special_x[3],
+                            uint64_t shift_inv)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!out || !pol || !special_x) return fail(GLP_E_ARG, "glp_fri_fold: NULL pointer");
+    if (pol_bits > 32) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    if (step_bits > pol_bits || pol_bits - step_bits > FRI_MAX_RED_BITS) return fail(GLP_E_ARG, "glp_fri_fold: reduction must be between 2^0 and 2^6");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t n_in = 1ull << pol_bits, n_out = 1ull << step_bits;
+    const gl_t *din = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, pol, (size_t)n_in * 3, &din));
+    const bool out_dev = on_device(out);
+    gl_t *dout = (gl_t *)out;
+    if (!out_dev) { GLP(ensure(ctx, ctx->tmp_out, (size_t)n_out * 3 * sizeof(gl_t))); dout = (gl_t *)ctx->tmp_out.p; }
+    FriFold a;
+    a.out = dout;
+    a.in = din;
+    a.pol_bits = pol_bits;
+    a.red_bits = pol_bits - step_bits;
+    for (int d = 0; d < 3; d++) a.x[d] = special_x[d];
+    a.shift_inv = shift_inv;
+    a.wi = gl_canon(gl_inv(host_root(pol_bits)));
+    a.wnx_inv = gl_canon(gl_inv(host_root(a.red_bits)));
+    a.nx_inv = host_ninv(a.red_bits);
+    LAUNCH_FLAT(ctx, k_fri_fold, (unsigned)((n_out + 127) / 128), 128, a);
+    CU(cudaGetLastError());
+    if (!out_dev) CU(cudaMemcpyAsync(out, dout, (size_t)n_out * 3 * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
+// The Merkle tree of a FRI layer (friProve.cpp:110-123,252-270): the folded polynomial (pol_n = 2^pol_bits elements)
+// regrouped by getTransposed into 2^next_bits rows of pol_n / 2^next_bits elements (`aux`, the tree's source), and
+// MerkleTreeGL over those rows.  aux / tree / root may be NULL when not wanted.
+extern "C" int glp_fri_group_tree(glp_ctx *ctx, uint64_t *aux, uint64_t *tree, uint64_t root[4], const uint64_t *pol, uint32_t pol_bits,
+                                  uint32_t next_bits)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!pol) return fail(GLP_E_ARG, "glp_fri_group_tree: pol is NULL");
+    if (pol_bits > 32) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
+    if (next_bits > pol_bits) return fail(GLP_E_ARG, "glp_fri_group_tree: more groups than elements");
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t pol_n = 1ull << pol_bits, rows = 1ull << next_bits, width = 3 * (pol_n >> next_bits);
+    const size_t tree_words = glp_tree_num_elements(rows);
+    const gl_t *dpol = nullptr;
+    GLP(stage_in(ctx, ctx->tmp_in, pol, (size_t)pol_n * 3, &dpol));
+    const bool aux_dev = on_device(aux), tree_dev = on_device(tree);
+    gl_t *daux = (gl_t *)aux;
+    if (!aux_dev) { GLP(ensure(ctx, ctx->tmp_out, (size_t)pol_n * 3 * sizeof(gl_t))); daux = (gl_t *)ctx->tmp_out.p; }
+    gl_t *dtree = (gl_t *)tree;
+    if (!tree_dev) { GLP(ensure(ctx, ctx->nodes, tree_words * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
+    const uint64_t nb = (pol_n + 255) / 256;
+    LAUNCH_FLAT(ctx, k_fri_transpose, (unsigned)(nb > 148 * 32 ? 148 * 32 : nb), 256, daux, dpol, pol_n, next_bits);
+    CU(cudaGetLastError());
+    if (aux && !aux_dev) CU(cudaMemcpyAsync(aux, daux, (size_t)pol_n * 3 * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    GLP(dev_merkletree(ctx, dtree, daux, width, width, rows));
+    if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------
