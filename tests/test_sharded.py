@@ -1,4 +1,4 @@
-"""Multi-GPU commit (xlayer_prover_b200/sharded.py) on the CPU: world_size 1, 2 and 4 gloo ranks, each driving the
+"""Multi-GPU commit (xlayer_prover_b200/sharded.py) on the CPU: world_size 1, 2, 4 and 8 gloo ranks, each driving the
 host-thread emulator build of the kernels.  The extension slabs, every Merkle node and the root must equal the
 single-device oracle result for every world size (results identical for every G)."""
 import os
@@ -37,7 +37,7 @@ def test_column_bounds_and_assemble():
     assert full[off: off + 16].tolist() == [24, 25, 26, 27, 1024, 1025, 1026, 1027, 2024, 2025, 2026, 2027, 3024, 3025, 3026, 3027]
 
 
-@pytest.mark.parametrize("world", [1, 2, 4])
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
 def test_sharded_commit_gloo(emu_built, oracle, tmp_path, world):
     from xlayer_prover_b200._capi import synth_matrix
     log_n, blow, ncols = 5, 1, 20
