@@ -203,8 +203,11 @@ def main_reference(args):
         "value": base["value"], "unit": "Melem/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": base["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d, extendPol + merkletree (CPU sample: %d cols)"
-                               % (args.log_rows, args.cols, args.log_rows + args.log_blowup, base["sample_cols"])},
+        "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
+                               % (args.log_rows, args.cols, args.log_rows + args.log_blowup),
+                   "parallelism": "host CPU, OpenMP x%d" % base["cores"], "seed": hex(SEED),
+                   "cpu_sample": "every step times %d of the %d columns at the full 2^%d rows (both stages are linear in the column count)"
+                                 % (base["sample_cols"], args.cols, args.log_rows)},
         "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": base["value"], "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "poseidon_hash_per_s": base["poseidon_hash_per_s"], "gpu_launches": 0,
