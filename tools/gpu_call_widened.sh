@@ -1,0 +1,10 @@
+#!/bin/bash
+# GPU call: parity tests, the widened-row sweep (quotient commit, FRI layers, constant tree) and its ncu launch list
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+tail -4 gpurun_out/pytest_gpu.log
+timeout 600 python tools/sweep.py widened > gpurun_out/sweep_widened.jsonl 2> gpurun_out/sweep_widened.err; echo "sweep rc=$?"
+cat gpurun_out/sweep_widened.jsonl; tail -5 gpurun_out/sweep_widened.err
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none --csv --log-file gpurun_out/launches_widened.csv \
+  python tools/sweep.py widened > gpurun_out/ncu_widened.log 2>&1; echo "ncu rc=$?"
+python __graft_entry__.py smoke 2>&1 | tail -2

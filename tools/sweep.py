@@ -5,6 +5,8 @@
     algorithmic bytes = 16 B per element per transform (read once, write once);
   * linear_hash over 2^24 leaves x {12, 16, 64, 128, 256, 660} columns: permutations/s and GB/s;
   * commits: configs[2] (2^20 x 200, blowup 8), recursive shapes (2^17 x 18 x8, 2^20 x 18 x4), cm4-like 2^23 x 6 x2.
+  * widened rows: step-4 quotient commit 2^23 -> 2^24 (qDim 3, qDeg 2), FRI folds 2^24 -> 2^19 -> 2^14 with their
+    layer trees, constant tree 2^20 x 100 (blowup 2); device-resident buffers.
 Timing: CUDA events on the launching stream, 2 warm-ups, best of 5; inputs are larger than L2 from 2^24 elements up
 (smaller cases are flagged "fits L2").  Prints one JSON object per line."""
 import json
@@ -94,4 +96,44 @@ if not only or "commit" in only:
              lde_algorithmic_GBps=round(8.0 * ncols * (n + ne) / ((prof["intt"][0] + prof["ntt_ext"][0]) / k) / 1e6, 1))
         del src, ext, tree
         torch.cuda.empty_cache()
+if not only or "widened" in only:
+    n, ne, qdim, qdeg = 1 << 23, 1 << 24, 3, 2
+    q = torch.empty(ne * qdim, dtype=torch.int64, device=dev)
+    cm4 = torch.empty(ne * qdim * qdeg, dtype=torch.int64, device=dev)
+    tree = torch.empty(tree_num_elements(ne), dtype=torch.int64, device=dev)
+    ctx.synth_fill(q, ne, qdim, 0xABCD)
+    ctx.get_profile()
+    ctx.set_profiling(True)
+    ms = timed(lambda: ctx.quotient_commit(cm4, tree, q, n, ne, qdim, qdeg), reps=3, warm=1)
+    ctx.set_profiling(False)
+    prof = ctx.get_profile()
+    k = max(1, prof["leaf_hash"][1])
+    byts = 8.0 * (ne * qdim + ne * qdim * qdeg)                    # quotient read once, cm4 written once
+    emit(kind="quotient_commit", log_n=23, log_n_ext=24, qdim=qdim, qdeg=qdeg, ms=round(ms, 3), stage_ms={s_: round(v[0] / k, 3) for s_, v in prof.items()},
+         transforms_algorithmic_GBps=round(byts / ((prof["intt"][0] + prof["ntt_ext"][0]) / k) / 1e6, 1),
+         note="stage intt = INTT(2^24 x 3) + chunk scaling, ntt_ext = NTT(2^24 x 6, 2^23 live rows)")
+    del q, cm4, tree
+    torch.cuda.empty_cache()
+    bits, pol = 24, torch.empty((1 << 24) * 3, dtype=torch.int64, device=dev)
+    ctx.synth_fill(pol, 1 << 24, 3, 0xF00D)
+    shift_inv = pow(7, 0xFFFFFFFF00000001 - 2, 0xFFFFFFFF00000001)
+    for nb, nxt in ((19, 14), (14, 9)):
+        out = torch.empty((1 << nb) * 3, dtype=torch.int64, device=dev)
+        ms = timed(lambda: ctx.fri_fold(out, pol, bits, nb, [3, 5, 7], shift_inv))
+        gbs = 24.0 * ((1 << bits) + (1 << nb)) / ms / 1e6
+        aux = torch.empty((1 << nb) * 3, dtype=torch.int64, device=dev)
+        ltree = torch.empty(tree_num_elements(1 << nxt), dtype=torch.int64, device=dev)
+        ms2 = timed(lambda: ctx.fri_group_tree(aux, ltree, out, nb, nxt))
+        emit(kind="fri_layer", pol_bits=bits, step_bits=nb, next_bits=nxt, fold_ms=round(ms, 4), fold_GBps=round(gbs, 1), fold_frac_of_measured_hbm=round(gbs / HBM, 4),
+             fits_l2=bool(24 * (1 << bits) < 126e6), layer_tree_ms=round(ms2, 4), layer_tree_perms=(1 << nxt) * ((3 * (1 << (nb - nxt)) + 7) // 8) + (1 << nxt) - 1)
+        pol, bits = out, nb
+        del aux, ltree
+    del pol
+    torch.cuda.empty_cache()
+    n, ne, npols = 1 << 20, 1 << 21, 100
+    src = torch.empty(n * npols, dtype=torch.int64, device=dev)
+    ct = torch.empty(2 + ne * npols + tree_num_elements(ne), dtype=torch.int64, device=dev)
+    ctx.synth_fill(src, n, npols, 0xC0DE)
+    ms = timed(lambda: ctx.const_tree(ct, src, n, ne, npols), reps=3, warm=1)
+    emit(kind="const_tree", log_n=20, log_n_ext=21, npols=npols, ms=round(ms, 3), melem_per_s=round(n * npols / ms / 1e3, 1))
 ctx.close()

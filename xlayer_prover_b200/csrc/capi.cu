@@ -1450,7 +1450,9 @@ extern "C" int glp_fri_fold(glp_ctx *ctx, uint64_t *out, const uint64_t *pol, ui
     a.wi = gl_canon(gl_inv(host_root(pol_bits)));
     a.wnx_inv = gl_canon(gl_inv(host_root(a.red_bits)));
     a.nx_inv = host_ninv(a.red_bits);
-    LAUNCH_FLAT(ctx, k_fri_fold, (unsigned)((n_out + 127) / 128), 128, a);
+    const size_t smem = fri_fold_smem(a.red_bits);
+    if (smem > 48 * 1024) GLP_SET_SMEM(k_fri_fold, smem);
+    LAUNCH(ctx, k_fri_fold, (unsigned)((n_out + FRI_THREADS - 1) / FRI_THREADS), FRI_THREADS, smem, a);
     CU(cudaGetLastError());
     if (!out_dev) CU(cudaMemcpyAsync(out, dout, (size_t)n_out * 3 * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));

@@ -40,25 +40,36 @@ struct FriFold {
     gl_t nx_inv;                     // 1 / nX
 };
 
-__global__ void __launch_bounds__(128)
+// The nX x 3 values of a thread live in shared memory, element (d, i) of thread t at v[(d*nX + i)*FRI_THREADS + t]
+// (consecutive threads in consecutive words: conflict-free), because indexing them with the loop variables of the
+// butterfly network would put a per-thread array in local memory -- a first version did, and moved 13x the
+// algorithmic bytes through DRAM (profiles/r01_launches_widened.txt).  64 threads x 64 x 3 words = 96 KB at nX = 64.
+#define FRI_THREADS 64
+static inline size_t fri_fold_smem(uint32_t red_bits) { return ((size_t)3 * FRI_THREADS + 1) * ((size_t)1 << red_bits) * sizeof(gl_t); }
+
+__global__ void __launch_bounds__(FRI_THREADS)
 k_fri_fold(FriFold a)
 {
+    GLP_DYN_SMEM(gl_t, sm);
     const uint64_t pol2n = 1ull << (a.pol_bits - a.red_bits);
-    const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= pol2n) return;
-    const uint32_t nx = 1u << a.red_bits;
-    gl_t v[3][1 << FRI_MAX_RED_BITS];
-    gl_t tw[1 << (FRI_MAX_RED_BITS - 1)];                       // w_nX^-j, j < nX/2
+    const uint32_t nx = 1u << a.red_bits, t = threadIdx.x;
+    gl_t *v = sm + t;                                             // v[(d*nx + i) * FRI_THREADS]
+    gl_t *tw = sm + (size_t)3 * nx * FRI_THREADS;                 // w_nX^-j, j < nX/2, shared by the CTA
+    uint64_t g = (uint64_t)blockIdx.x * FRI_THREADS + t;
+    const bool live = g < pol2n;
+    if (!live) g = pol2n - 1;
+#define FRI_V(d, i) v[((size_t)(d) * nx + (i)) * FRI_THREADS]
     // gather, bit-reversed, so that the decimation-in-time loop below ends in natural order
     for (uint32_t i = 0; i < nx; i++) {
         const uint32_t r = a.red_bits ? (__brev(i) >> (32 - a.red_bits)) : 0;
         const gl_t *p = a.in + ((uint64_t)i * pol2n + g) * 3;
-        v[0][r] = p[0]; v[1][r] = p[1]; v[2][r] = p[2];
+        FRI_V(0, r) = p[0]; FRI_V(1, r) = p[1]; FRI_V(2, r) = p[2];
     }
-    {
-        gl_t t = 1;
-        for (uint32_t j = 0; j < nx / 2; j++) { tw[j] = t; t = gl_mul(t, a.wnx_inv); }
+    if (t == 0) {
+        gl_t w = 1;
+        for (uint32_t j = 0; j < nx / 2; j++) { tw[j] = w; w = gl_mul(w, a.wnx_inv); }
     }
+    __syncthreads();
     // c[i] = 1/nX * sum_k v[k] * w_nX^(-i k)   (NTT_Goldilocks::INTT, ntt_goldilocks.cpp:307-324)
     for (uint32_t half = 1, s = a.red_bits; half < nx; half <<= 1) {
         s--;                                                      // twiddle stride: w_(2 half)^-j = w_nX^-(j << s)
@@ -67,29 +78,32 @@ k_fri_fold(FriFold a)
                 const gl_t w = tw[j << s];
 #pragma unroll
                 for (int d = 0; d < 3; d++) {
-                    const gl_t u = v[d][base + j], t = gl_mul(v[d][base + j + half], w);
-                    v[d][base + j] = gl_add(u, t);
-                    v[d][base + j + half] = gl_sub(u, t);
+                    const gl_t u = FRI_V(d, base + j), x = gl_mul(FRI_V(d, base + j + half), w);
+                    FRI_V(d, base + j) = gl_add(u, x);
+                    FRI_V(d, base + j + half) = gl_sub(u, x);
                 }
             }
     }
-    // coefficient i times (1/nX) * sinv_g^i, then Horner at special_x from the top coefficient down
+    // coefficient i times (1/nX) * sinv_g^i (polMulAxi), then Horner at special_x from the top coefficient down (evalPol)
     const gl_t sinv = gl_mul(a.shift_inv, gl_pow(a.wi, g));
     gl_t r = a.nx_inv;
     for (uint32_t i = 0; i < nx; i++) {
 #pragma unroll
-        for (int d = 0; d < 3; d++) v[d][i] = gl_mul(v[d][i], r);
+        for (int d = 0; d < 3; d++) FRI_V(d, i) = gl_mul(FRI_V(d, i), r);
         r = gl_mul(r, sinv);
     }
-    gl_t res[3] = {v[0][nx - 1], v[1][nx - 1], v[2][nx - 1]};
+    gl_t res[3] = {FRI_V(0, nx - 1), FRI_V(1, nx - 1), FRI_V(2, nx - 1)};
     for (int i = (int)nx - 2; i >= 0; i--) {
-        gl_t t[3];
-        gl3_mul(t, res, a.x);
+        gl_t m[3];
+        gl3_mul(m, res, a.x);
 #pragma unroll
-        for (int d = 0; d < 3; d++) res[d] = gl_add(t[d], v[d][i]);
+        for (int d = 0; d < 3; d++) res[d] = gl_add(m[d], FRI_V(d, i));
     }
+#undef FRI_V
+    if (live) {
 #pragma unroll
-    for (int d = 0; d < 3; d++) a.out[g * 3 + d] = gl_canon(res[d]);
+        for (int d = 0; d < 3; d++) a.out[g * 3 + d] = gl_canon(res[d]);
+    }
 }
 
 // aux[(i*h + j)*3 ..] = pol[(j*w + i)*3 ..],  i < w = 2^next_bits, j < h = pol_n / w
