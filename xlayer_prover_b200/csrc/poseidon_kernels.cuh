@@ -46,8 +46,15 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 // (every block but the last a multiple of 8 columns); cap_in may alias out.
 // LOCKSTEP: every thread of the CTA runs the same number of permutations (rows past the end are clamped to the
 // last row and simply not stored), so the per-round barriers inside pos_permute_t are reached by all.
+// POS_LEAF_MINBLOCKS (optional): second argument of __launch_bounds__, i.e. a register cap (6 -> 80 registers, 4 -> 128);
+// without it ptxas settles at 96 registers = 5 CTAs of 128 threads per SM
+#ifdef POS_LEAF_MINBLOCKS
+#define POS_LEAF_BOUNDS __launch_bounds__(POS_LEAF_BLOCK, POS_LEAF_MINBLOCKS)
+#else
+#define POS_LEAF_BOUNDS __launch_bounds__(POS_LEAF_BLOCK)
+#endif
 template <bool LOCKSTEP>
-__global__ void __launch_bounds__(POS_LEAF_BLOCK)
+__global__ void POS_LEAF_BOUNDS
 k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in,
                    uint64_t out_pitch)
 {
