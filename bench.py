@@ -184,7 +184,20 @@ def run_cpu_baseline(args, budget_s, nsteps=1, warmup=0):
         lde.append(tl)
         mt.append(tm)
     t = (sum(lde) + sum(mt)) / len(times)        # the reference's own two calls; numpy buffer allocation excluded
+    # the reference's AVX-512 build on the same sample, when the host has the instructions ("also reported");
+    # the headline CPU number stays the AVX2 build, the reference's default (Makefile:19)
+    avx512 = None
+    try:
+        from oracle import refbind
+        has512 = any("avx512f" in l for l in open("/proc/cpuinfo") if l.startswith("flags"))
+        o512 = refbind.reference(avx512=True) if (kind == "reference" and has512) else None
+        if o512 is not None:
+            _, tl, tm, _ = cpu_commit_step(o512, a, n_ext)
+            avx512 = {"value": n * c / (tl + tm) / 1e6, "unit": "Melem/s", "extendPol_s": tl, "merkletree_s": tm}
+    except Exception as ex:                                              # a baseline extra must never take the bench down
+        avx512 = {"error": repr(ex)}
     return {
+        "avx512_build": avx512,
         "value": n * c / t / 1e6, "unit": "Melem/s", "cores": cores, "kind": kind,
         "sample": "2^%d rows x %d of %d columns, blowup %d, %d timed step(s); extendPol %.2f s + merkletree %.2f s per step"
                   % (args.log_rows, c, args.cols, 1 << args.log_blowup, nsteps, sum(lde) / len(lde), sum(mt) / len(mt)),
@@ -208,7 +221,7 @@ def main_reference(args):
                    "parallelism": "host CPU, OpenMP x%d" % base["cores"], "seed": hex(SEED),
                    "cpu_sample": "every step times %d of the %d columns at the full 2^%d rows (both stages are linear in the column count)"
                                  % (base["sample_cols"], args.cols, args.log_rows)},
-        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "avx512_build")},
         "e2e": {"value": base["value"], "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "poseidon_hash_per_s": base["poseidon_hash_per_s"], "gpu_launches": 0,
     }
@@ -384,6 +397,7 @@ def main_ours(args):
                        "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d whose last NTT pass stores into the peers' row slabs over NVLink (fused exchange) -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
                        "seed": hex(SEED)},
             "commit_ms": result["ms_per_step"], "poseidon_hash_per_s": perms / sec,
+            "leaf_hash_rows_per_s": (R / (leaf_ms * 1e-3)) if leaf_ms > 0 else None,
             "stage_ms": {"intt": prof["intt"][0] / K, "ntt_ext": prof["ntt_ext"][0] / K, "leaf_hash": prof["leaf_hash"][0] / K,
                          "tree_levels": prof["tree_levels"][0] / K, "note": "rank 0, per step, CUDA events on the launching stream"},
             "roofline": {"kernel": "k_linear_hash_rows", "bound": "hbm", "achieved": leaf_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -410,7 +424,7 @@ def main_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             try:
                 base = run_cpu_baseline(args, args.cpu_budget_s)
-                line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
+                line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "avx512_build")}
             except Exception as ex:
                 line["cpu_baseline"] = {"error": repr(ex)}
         emit(line)

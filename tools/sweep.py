@@ -7,6 +7,8 @@
   * commits: configs[2] (2^20 x 200, blowup 8), recursive shapes (2^17 x 18 x8, 2^20 x 18 x4), cm4-like 2^23 x 6 x2.
   * widened rows: step-4 quotient commit 2^23 -> 2^24 (qDim 3, qDeg 2), FRI folds 2^24 -> 2^19 -> 2^14 with their
     layer trees, constant tree 2^20 x 100 (blowup 2); device-resident buffers.
+  * data independence: config B/2 (2^23 x 330, blowup 2) on uniform inputs and on a "trace-like" distribution
+    (50 % zeros, ~30 % below 2^16, ~20 % uniform).
 Timing: CUDA events on the launching stream, 2 warm-ups, best of 5; inputs are larger than L2 from 2^24 elements up
 (smaller cases are flagged "fits L2").  Prints one JSON object per line."""
 import json
@@ -96,6 +98,33 @@ if not only or "commit" in only:
              lde_algorithmic_GBps=round(8.0 * ncols * (n + ne) / ((prof["intt"][0] + prof["ntt_ext"][0]) / k) / 1e6, 1))
         del src, ext, tree
         torch.cuda.empty_cache()
+if not only or "dist" in only:
+    n, ne, ncols = 1 << 23, 1 << 24, 330
+    src = torch.empty(n * ncols, dtype=torch.int64, device=dev)
+    ext = torch.empty(ne * ncols, dtype=torch.int64, device=dev)
+    tree = torch.empty(tree_num_elements(ne), dtype=torch.int64, device=dev)
+    roots = {}
+    for dist_name in ("uniform", "trace-like"):
+        ctx.synth_fill(src, n, ncols, 0x9E3779B97F4A7C15 + 2)
+        if dist_name == "trace-like":
+            step = 1 << 26
+            for o in range(0, src.numel(), step):               # in place, chunked: selector = 4 hashed bits of the value
+                v = src[o:o + step]
+                sel = ((v * -7046029254386353131) >> 60) & 15
+                v.copy_(torch.where(sel < 8, torch.zeros_like(v), torch.where(sel < 13, v & 0xFFFF, v)))
+            torch.cuda.synchronize()
+        zeros = float((src[: 1 << 24] == 0).float().mean().item())
+        ctx.get_profile()
+        ctx.set_profiling(True)
+        ms = timed(lambda: ctx.commit(ext, tree, src, n, ne, ncols), reps=3, warm=1)
+        ctx.set_profiling(False)
+        prof = ctx.get_profile()
+        k = max(1, prof["leaf_hash"][1])
+        emit(kind="data_independence", distribution=dist_name, log_rows=23, ncols=ncols, blowup=2, zero_fraction=round(zeros, 3), ms=round(ms, 3),
+             stage_ms={s_: round(v_[0] / k, 3) for s_, v_ in prof.items()}, root0=hex(int(tree[-4].item()) & 0xFFFFFFFFFFFFFFFF))
+    del src, ext, tree
+    torch.cuda.empty_cache()
+
 if not only or "widened" in only:
     n, ne, qdim, qdeg = 1 << 23, 1 << 24, 3, 2
     q = torch.empty(ne * qdim, dtype=torch.int64, device=dev)
