@@ -19,6 +19,11 @@ shape = st.tuples(st.integers(0, 9), st.integers(1, 41), st.integers(0, 4), st.i
 def one_case(ctx, oracle, logn, ncols, logb, seed, device):
     rng = np.random.default_rng(seed)
     n = 1 << logn
+    if (n << logb) == 4 and n < 4:
+        # the reference build itself aborts inside extendPol for N = 1 or 2 extended to exactly 4 rows (its phase
+        # split degenerates); these two shapes are checked against the pinned C restatement instead
+        from oracle import refbind
+        oracle = refbind.port()
     a = edge_matrix(rng, n, ncols)
     check_commit(ctx, oracle, a, n << logb, device=device)
     check_equal(run_ntt(ctx, a, True, False), oracle.canonical(oracle.ntt(a, inverse=True)), "INTT %s" % ((n, ncols),))
