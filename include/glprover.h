@@ -54,6 +54,10 @@ int glp_device_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr);
 int glp_device_free(glp_ctx *ctx, void *ptr);
 int glp_host_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr);     /* pinned */
 int glp_host_free(glp_ctx *ctx, void *ptr);
+/* pin / unpin memory the caller owns (e.g. the prover's polynomial buffer, src/prover/prover.cpp:101-115), so that the
+ * host-pointer entry points below copy at the pinned rate */
+int glp_host_register(glp_ctx *ctx, void *ptr, uint64_t bytes);
+int glp_host_unregister(glp_ctx *ctx, void *ptr);
 int glp_memcpy(glp_ctx *ctx, void *dst, const void *src, uint64_t bytes);   /* any direction, synchronous */
 int glp_mem_info(glp_ctx *ctx, uint64_t *free_bytes, uint64_t *total_bytes);
 

@@ -74,6 +74,9 @@ cudaError_t cudaMalloc(void **p, size_t n);
 cudaError_t cudaFree(void *p);
 cudaError_t cudaHostAlloc(void **p, size_t n, unsigned flags);
 cudaError_t cudaFreeHost(void *p);
+enum { cudaHostRegisterPortable = 1 };
+static inline cudaError_t cudaHostRegister(void *, size_t, unsigned) { return cudaSuccess; }
+static inline cudaError_t cudaHostUnregister(void *) { return cudaSuccess; }
 cudaError_t cudaMemcpy(void *d, const void *s, size_t n, cudaMemcpyKind k);
 cudaError_t cudaMemcpyAsync(void *d, const void *s, size_t n, cudaMemcpyKind k, cudaStream_t st);
 cudaError_t cudaMemcpy2DAsync(void *d, size_t dp, const void *s, size_t sp, size_t w, size_t h, cudaMemcpyKind k, cudaStream_t st);

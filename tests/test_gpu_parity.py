@@ -515,6 +515,25 @@ def test_fri_layers(ctx, reference, rng):
     check_fri_layers(ctx, reference, rng, pol_bits=20, steps=(15, 10, 5))
 
 
+def test_host_register(ctx, oracle, rng):
+    """glp_host_register: the caller's own (page-aligned here) buffers pinned in place, commit through them, unpinned"""
+    n, c = 1 << 12, 24
+    a = edge_matrix(rng, n, c)
+    ext, tree = np.zeros((2 * n, c), dtype=np.uint64), np.zeros(tree_words(2 * n), dtype=np.uint64)
+    for buf in (a, ext, tree):
+        ctx.host_register(buf)
+    try:
+        root = ctx.commit(ext, tree, a, n, 2 * n, c)
+    finally:
+        for buf in (a, ext, tree):
+            ctx.host_unregister(buf)
+    want_ext = oracle.extend_pol(a, 2 * n)
+    want_tree = oracle.merkletree(want_ext)
+    check_equal(ext, want_ext, "registered ext")
+    check_equal(tree, want_tree, "registered tree")
+    check_equal(root, want_tree[-4:], "registered root")
+
+
 def test_overlapped_commit_knob(oracle, rng):
     """GLP_CO=1: LDE of column block k+1 (k_ntt_pass_co) under the leaf hash of block k -- off by default (slower,
     profiles/r01_overlap_experiment.txt) but it must give the same bits.  2^14 rows so that the tiles are two-step."""

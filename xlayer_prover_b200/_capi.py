@@ -31,6 +31,8 @@ SIGNATURES = {
     "glp_device_free": (i32, [vp, vp]),
     "glp_host_alloc": (i32, [vp, u64, C.POINTER(vp)]),
     "glp_host_free": (i32, [vp, vp]),
+    "glp_host_register": (i32, [vp, vp, u64]),
+    "glp_host_unregister": (i32, [vp, vp]),
     "glp_memcpy": (i32, [vp, vp, vp, u64]),
     "glp_mem_info": (i32, [vp, u64p, u64p]),
     "glp_ntt": (i32, [vp, vp, vp, u64, u64, i32, i32]),
@@ -161,6 +163,12 @@ class Context:
         return p.value
 
     def host_free(self, p): self.lib.check(self.lib.glp_host_free(self.h, p))
+    def host_register(self, a):
+        """pin an existing numpy array (glp_host_register); pair with host_unregister"""
+        self.lib.check(self.lib.glp_host_register(self.h, ptr_of(a), a.nbytes))
+
+    def host_unregister(self, a): self.lib.check(self.lib.glp_host_unregister(self.h, ptr_of(a)))
+
     def memcpy(self, dst, src, nbytes): self.lib.check(self.lib.glp_memcpy(self.h, ptr_of(dst), ptr_of(src), nbytes))
 
     def mem_info(self):

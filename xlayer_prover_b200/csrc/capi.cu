@@ -237,6 +237,22 @@ extern "C" int glp_host_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr)
     return GLP_OK;
 }
 extern "C" int glp_host_free(glp_ctx *ctx, void *ptr) { (void)ctx; if (ptr) CU(cudaFreeHost(ptr)); return GLP_OK; }
+// Pin memory the caller already owns (the prover's big polynomial buffer, src/prover/prover.cpp:101-115, is malloc'ed or
+// mmap'ed once and reused for every proof): copies to and from it then run at the pinned rate (52-57 GB/s instead of
+// 11-21 GB/s pageable, profiles/r01_pcie_probe.txt).  The range stays usable as ordinary memory.
+extern "C" int glp_host_register(glp_ctx *ctx, void *ptr, uint64_t bytes)
+{
+    if (!ctx || !ptr || !bytes) return fail(GLP_E_ARG, "glp_host_register: NULL argument");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+    return GLP_OK;
+}
+extern "C" int glp_host_unregister(glp_ctx *ctx, void *ptr)
+{
+    if (!ctx || !ptr) return fail(GLP_E_ARG, "glp_host_unregister: NULL argument");
+    CU(cudaHostUnregister(ptr));
+    return GLP_OK;
+}
 extern "C" int glp_memcpy(glp_ctx *ctx, void *dst, const void *src, uint64_t bytes)
 {
     if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
