@@ -263,6 +263,20 @@ def test_fri_layers(ectx, reference, rng):
     check_fri_layers(ectx, reference, rng, pol_bits=7, steps=(1, 0))            # folds by 2^6 and 2^1, down to a constant
 
 
+def test_merkletree_streamed_host_source(emu_lib, oracle, rng):
+    """host-resident source above GLP_MERKLE_STREAM_MIN: uploaded in row blocks under the leaf hash (8 blocks of 1024 rows)"""
+    os.environ["GLP_MERKLE_STREAM_MIN"] = "65536"
+    try:
+        c = make_ctx(emu_lib)
+    finally:
+        os.environ.pop("GLP_MERKLE_STREAM_MIN", None)
+    a = edge_matrix(rng, 8192, 20)
+    launches0 = c.launch_count()
+    check_equal(run_merkletree(c, a), oracle.canonical(oracle.merkletree(a)), "streamed merkletree")
+    assert c.launch_count() - launches0 >= 8
+    c.close()
+
+
 def test_argument_errors(ectx):
     from xlayer_prover_b200._capi import GLP_E_ARG, GLP_E_DOMAIN, GlpError
     a = np.zeros((12, 2), dtype=np.uint64)

@@ -515,6 +515,17 @@ def test_fri_layers(ctx, reference, rng):
     check_fri_layers(ctx, reference, rng, pol_bits=20, steps=(15, 10, 5))
 
 
+def test_merkletree_streamed_host_source(oracle, rng):
+    """MerkleTreeGL::merkelize on a host-resident source: row blocks uploaded under the leaf hash"""
+    c = env_ctx(GLP_MERKLE_STREAM_MIN=1 << 20)
+    try:
+        for n, w in ((1 << 15, 100), (1 << 13, 660), (1 << 16, 5)):
+            a = edge_matrix(rng, n, w)
+            check_equal(run_merkletree(c, a), oracle.canonical(oracle.merkletree(a)), "streamed merkletree %s" % ((n, w),))
+    finally:
+        c.close()
+
+
 def test_host_register(ctx, oracle, rng):
     """glp_host_register: the caller's own (page-aligned here) buffers pinned in place, commit through them, unpinned"""
     n, c = 1 << 12, 24

@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
 """e2e (host-pointer) commit at the bench shape for several pipeline block widths; prints ms per commit and,
 with GLP_TRACE=1, the pipeline timeline.  usage: e2e_probe.py [log_rows] [cols] width [width ...]
-E2E_MODE=full (default: extension + tree to the host) | root (no download at all) | tree (tree only)"""
+E2E_MODE=full (default: extension + tree to the host) | root (no download at all) | tree (tree only)
+        | separate (the reference's unchanged call sequence: extendPol host -> host, then merkelize on the host-resident extension)"""
 import ctypes
 import os
 import sys
@@ -31,7 +32,17 @@ for w in widths:
     for it in range(3):
         t0 = time.perf_counter()
         mode = os.environ.get("E2E_MODE", "full")
-        roots.append(c.commit(hext if mode == "full" else None, None if mode == "root" else htree, hin, n, n_ext, C))
+        if mode == "separate":
+            c.extend_pol(hext, hin, n_ext, n, C)
+            t1 = time.perf_counter()
+            c.merkletree(htree, hext, C, n_ext)
+            t2 = time.perf_counter()
+            print("   extendPol %.1f ms, merkelize %.1f ms" % ((t1 - t0) * 1e3, (t2 - t1) * 1e3), flush=True)
+            r4 = np.zeros(4, dtype=np.uint64)
+            c.memcpy(r4, htree + 8 * (tree_num_elements(n_ext) - 4), 32)
+            roots.append(r4)
+        else:
+            roots.append(c.commit(hext if mode == "full" else None, None if mode == "root" else htree, hin, n, n_ext, C))
         dt = time.perf_counter() - t0
         print("width %4d  iter %d  %8.1f ms  root[0] %#x" % (w, it, dt * 1e3, int(roots[-1][0])), flush=True)
     c.close()

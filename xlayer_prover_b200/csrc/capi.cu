@@ -61,6 +61,7 @@ struct glp_ctx {
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
+    uint64_t merkle_stream_min = 0;          // GLP_MERKLE_STREAM_MIN: bytes from which a host-resident Merkle source is uploaded block by block (tests lower it)
     bool stage_all = true;                   // GLP_STAGE_ALL=0: two alternating upload buffers even when the whole input fits
     bool no_narrow = false;                  // GLP_NTT_NO_NARROW=1: lane = column even for matrices of <= 16 columns (comparison runs)
     bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
@@ -177,6 +178,8 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_narrow = nn && atoi(nn) != 0;
     const char *tr = getenv("GLP_TRACE");
     ctx->trace = tr && atoi(tr) != 0;
+    const char *msm = getenv("GLP_MERKLE_STREAM_MIN");
+    if (msm && atoll(msm) > 0) ctx->merkle_stream_min = (uint64_t)atoll(msm);
     const char *sa = getenv("GLP_STAGE_ALL");
     if (sa) ctx->stage_all = atoi(sa) != 0;
     const char *sc = getenv("GLP_STREAM_COLS");
@@ -1027,6 +1030,52 @@ extern "C" int glp_linear_hash_absorb(glp_ctx *ctx, uint64_t *state4, const uint
     return GLP_OK;
 }
 
+// Host-resident source (what MerkleTreeGL::merkelize() hands over when starks.cpp is left unchanged): rows are independent
+// leaves, so the matrix is uploaded in contiguous row blocks of ~1 GB on a copy stream while the previous block is hashed;
+// the upload (52-57 GB/s) and the leaf hash (65 GB/s of input at 660 columns) overlap and two staging blocks replace a
+// device copy of the whole matrix.
+#define GLP_MERKLE_STREAM_MIN_BYTES ((uint64_t)256 << 20)
+static int merkletree_streamed(glp_ctx *ctx, gl_t *dtree, const uint64_t *in, uint64_t width, uint64_t nrows)
+{
+    const uint64_t target = ctx->merkle_stream_min ? ctx->merkle_stream_min / 4 + 1 : ((uint64_t)1 << 30);   // bytes per block
+    uint64_t rb = nrows;
+    while (rb > 1024 && rb * width * sizeof(gl_t) > target) rb >>= 1;
+    const uint64_t nblocks = nrows / rb;                                     // both powers of two
+    const size_t block_words = (size_t)rb * width;
+    GLP(ensure(ctx, ctx->tmp_in, 2 * block_words * sizeof(gl_t)));
+    gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + block_words};
+    std::vector<cudaEvent_t> up(nblocks), hashed(nblocks);
+    for (uint64_t k = 0; k < nblocks; k++) {
+        CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&hashed[k], cudaEventDisableTiming));
+    }
+    cudaEvent_t start;
+    CU(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    CU(cudaEventRecord(start, ctx->stream));                                  // the staging buffers may still be in use by earlier work
+    CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
+    int rc = GLP_OK;
+    {
+        ProfScope ps(ctx, 2);
+        for (uint64_t k = 0; k < nblocks && rc == GLP_OK; k++) {
+            if (k >= 2) CU(cudaStreamWaitEvent(ctx->copy_stream[0], hashed[k - 2], 0));
+            CU(cudaMemcpyAsync(stage[k & 1], in + k * block_words, block_words * sizeof(gl_t), cudaMemcpyHostToDevice, ctx->copy_stream[0]));
+            CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
+            CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
+            rc = dev_leaf_hash(ctx, dtree + 4 * k * rb, stage[k & 1], width, width, rb);
+            CU(cudaEventRecord(hashed[k], ctx->stream));
+        }
+    }
+    if (rc == GLP_OK) {
+        ProfScope ps(ctx, 3);
+        rc = dev_tree_levels(ctx, dtree, nrows);
+    }
+    cudaError_t e0 = cudaStreamSynchronize(ctx->copy_stream[0]);              // before the events go away
+    for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(hashed[k]); }
+    cudaEventDestroy(start);
+    CU(e0);
+    return rc;
+}
+
 extern "C" int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t dim)
 {
     if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
@@ -1036,12 +1085,17 @@ extern "C" int glp_merkletree(glp_ctx *ctx, uint64_t *tree, const uint64_t *in, 
     if (!is_pow2(nrows)) return fail(GLP_E_ARG, "glp_merkletree: nrows must be a power of two");
     CU(cudaSetDevice(ctx->device));
     const size_t tw = glp_tree_num_elements(nrows);
-    const gl_t *din = (const gl_t *)in;
-    if (width) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)nrows * width, &din));
     const bool out_dev = on_device(tree);
     gl_t *dtree = (gl_t *)tree;
     if (!out_dev) { GLP(ensure(ctx, ctx->nodes, tw * sizeof(gl_t))); dtree = (gl_t *)ctx->nodes.p; }
-    GLP(dev_merkletree(ctx, dtree, din, width, width, nrows));
+    const uint64_t stream_min = ctx->merkle_stream_min ? ctx->merkle_stream_min : GLP_MERKLE_STREAM_MIN_BYTES;
+    if (width > POS_CAP && !on_device(in) && nrows >= 2048 && nrows * width * sizeof(gl_t) >= stream_min) {
+        GLP(merkletree_streamed(ctx, dtree, in, width, nrows));
+    } else {
+        const gl_t *din = (const gl_t *)in;
+        if (width) GLP(stage_in(ctx, ctx->tmp_in, in, (size_t)nrows * width, &din));
+        GLP(dev_merkletree(ctx, dtree, din, width, width, nrows));
+    }
     if (!out_dev) CU(cudaMemcpyAsync(tree, dtree, tw * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return GLP_OK;
