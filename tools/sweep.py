@@ -79,9 +79,12 @@ if not only or "hash" in only:
         del src, out
         torch.cuda.empty_cache()
 
-if not only or "commit" in only:
+if not only or "commit" in only or "stages" in only:
     for name, logn, ncols, logb in (("configs[2] recursive/aggregation shape", 20, 200, 3), ("recursive1 cm1", 17, 18, 3), ("c12a cm1", 20, 18, 2),
-                                    ("zkevm cm4 (quotient)", 23, 6, 1), ("zkevm cm2", 23, 168, 1)):
+                                    ("zkevm cm4 (quotient)", 23, 6, 1), ("zkevm cm2", 23, 168, 1), ("zkevm cm3", 23, 408, 1),
+                                    ("zkevm cm1 (fork 9: 751 columns)", 23, 751, 1)):
+        if only and "stages" in only and not name.startswith("zkevm"):
+            continue
         n, ne = 1 << logn, 1 << (logn + logb)
         src = torch.empty(n * ncols, dtype=torch.int64, device=dev)
         ext = torch.empty(ne * ncols, dtype=torch.int64, device=dev)
