@@ -46,6 +46,9 @@ int glp_set_stream(glp_ctx *ctx, void *cuda_stream);
 int glp_synchronize(glp_ctx *ctx);
 /* kernels launched by this context so far (bench.py reports the difference as gpu_launches) */
 uint64_t glp_launch_count(const glp_ctx *ctx);
+/* leaf rows the hash kernel has had to redo with its exact arithmetic since the library was loaded (the fast path leaves a
+ * 2^-33-per-multiplication wrap uncorrected and detects it); synchronises the context.  Diagnostics only. */
+uint64_t glp_leaf_redo_rows(glp_ctx *ctx);
 /* cap on internal scratch in bytes (0 = default: a quarter of free device memory, at most 16 GiB) */
 int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes);
 

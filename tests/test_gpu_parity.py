@@ -80,6 +80,41 @@ def test_linear_hash_kat_and_sizes(ctx, oracle, golden, rng):
         check_equal(got, oracle.linear_hash_rows(np.ascontiguousarray(a[:, :size])), "linear_hash size %d" % size)
 
 
+def test_linear_hash_deferred_wrap_rows_are_redone(ctx, oracle, rng):
+    """The leaf kernel's fast path leaves the (lo64 of a product) < (its top word) wrap of a fold uncorrected and, when it
+    fires, hashes the row again with the exact fold (poseidon_kernels.cuh, POS_DEFER_BORROW).  On random data that is one
+    row in 10^5, so drive it: a state word y = a * 2^32 (a >= 2^16) squares to lo64 = 0, top word = a^2 >> 32 > 0 in the
+    first S-box layer.  Rows carry such a word at every rate position and in several sponge blocks."""
+    import re, pathlib
+    src = (pathlib.Path(__file__).resolve().parents[1] / "xlayer_prover_b200" / "csrc" / "poseidon_tables.cuh").read_text()
+    rc = [int(v, 16) for v in re.findall(r"0x[0-9a-fA-F]{16}", src.split("GLP_POSEIDON_RC_INIT", 1)[1])[:8]]
+    P = 0xFFFFFFFF00000001
+    ncols, nrows = 100, 4096
+    a = edge_matrix(rng, nrows, ncols)
+    crafted = []
+    for k, row in enumerate(range(5, nrows, 97)):
+        pos, blk = k % 8, (k // 8) % 12
+        y = (0xFFFFFFFE - k) << 32                        # canonical, above every round constant, low 32 bits zero
+        assert rc[pos] <= y < P
+        a[row, 8 * blk + pos] = y - rc[pos]               # + RC[pos] = y exactly
+        crafted.append(row)
+    want = oracle.linear_hash_rows(a)
+    before = ctx.leaf_redo_rows()
+    got = np.zeros((nrows, 4), dtype=np.uint64)
+    ctx.linear_hash_rows(got, a, ncols, ncols, nrows)
+    check_equal(got, want, "linear_hash with rows that take the exact path")
+    redone = ctx.leaf_redo_rows() - before
+    assert redone >= len(crafted), (redone, len(crafted))
+    # the same rows as leaves of a tree and through the sponge continuation (cap_in aliases out)
+    tree = run_merkletree(ctx, a, device=True)
+    check_equal(tree, oracle.merkletree(a), "merkletree with rows that take the exact path")
+    cap = np.zeros((nrows, 4), dtype=np.uint64)
+    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, :48]), 48, 48, nrows, first=True)
+    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, 48:]), ncols - 48, ncols - 48, nrows, first=False)
+    check_equal(cap, want, "absorb in two blocks with rows that take the exact path")
+    assert ctx.leaf_redo_rows() - before >= 3 * len(crafted)
+
+
 def test_merkletree_kats(ctx, golden):
     check_equal(run_merkletree(ctx, fib_matrix(64, 128))[-4:], golden["merkletree_64x128_root"]["out"], "64x128")
     check_equal(run_merkletree(ctx, fib_matrix(64, 128), device=True)[-4:], golden["merkletree_64x128_root"]["out"], "64x128 dev")

@@ -40,7 +40,9 @@ int main(int argc, char **argv)
     const double perms = (double)nrows * ((ncols + 7) / 8);
     cudaFuncAttributes fa;
     cudaFuncGetAttributes(&fa, k_linear_hash_rows<POS_LEAF_LOCKSTEP != 0>);
-    printf("%-44s block %4d regs %3d  %8.3f ms  %7.1f Mperm/s  checksum %016llx\n", tag, POS_LEAF_BLOCK, fa.numRegs, best, perms / best / 1e3,
-           (unsigned long long)gl_canon(ck));
+    unsigned long long redo = 0;
+    cudaMemcpyFromSymbol(&redo, g_pos_redo_rows, sizeof redo);
+    printf("%-44s block %4d regs %3d  %8.3f ms  %7.1f Mperm/s  checksum %016llx  redone rows %llu (6 launches)\n", tag, POS_LEAF_BLOCK,
+           fa.numRegs, best, perms / best / 1e3, (unsigned long long)gl_canon(ck), redo);
     return 0;
 }

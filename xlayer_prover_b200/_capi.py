@@ -26,6 +26,7 @@ SIGNATURES = {
     "glp_set_stream": (i32, [vp, vp]),
     "glp_synchronize": (i32, [vp]),
     "glp_launch_count": (u64, [vp]),
+    "glp_leaf_redo_rows": (u64, [vp]),
     "glp_set_scratch_limit": (i32, [vp, u64]),
     "glp_device_alloc": (i32, [vp, u64, C.POINTER(vp)]),
     "glp_device_free": (i32, [vp, vp]),
@@ -148,6 +149,7 @@ class Context:
     def set_stream(self, raw_stream): self.lib.check(self.lib.glp_set_stream(self.h, raw_stream))
     def synchronize(self): self.lib.check(self.lib.glp_synchronize(self.h))
     def launch_count(self): return self.lib.glp_launch_count(self.h)
+    def leaf_redo_rows(self): return int(self.lib.glp_leaf_redo_rows(self.h))
     def set_scratch_limit(self, nbytes): self.lib.check(self.lib.glp_set_scratch_limit(self.h, nbytes))
 
     def device_alloc(self, nbytes):

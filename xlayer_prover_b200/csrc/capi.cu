@@ -216,6 +216,17 @@ extern "C" int glp_synchronize(glp_ctx *ctx)
     return GLP_OK;
 }
 extern "C" uint64_t glp_launch_count(const glp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+extern "C" uint64_t glp_leaf_redo_rows(glp_ctx *ctx)
+{
+    unsigned long long n = 0;
+#if !defined(GLP_EMU)
+    if (!ctx || cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess ||
+        cudaMemcpyFromSymbol(&n, g_pos_redo_rows, sizeof n) != cudaSuccess) { cudaGetLastError(); return 0; }
+#else
+    (void)ctx;
+#endif
+    return n;
+}
 extern "C" int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes)
 {
     if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");

@@ -216,6 +216,37 @@ GL_HD gl_t gl_reduce128_wide(gl_t lo, gl_t hi)
     return gl_reduce128_t<false>(lo, hi);
 #endif
 }
+// The fold with its RARE wrap deferred.  (p1:p0) - p3 borrows only when the low 64 bits of a product are below p3 < 2^32:
+// probability 2^-33 per fold on anything but crafted data, yet its fix-up (three instructions) runs every time.  Here the
+// borrow is only COUNTED into `bf` (bf -= borrow, one instruction) and the value is left wrong when it happens; the
+// caller must redo its whole computation with the exact fold whenever bf != 0 (k_linear_hash_rows redoes the row).
+// (Variants measured and dropped, profiles/r01_poseidon_defer.txt: the gl_reduce128_wide form with ITS 2^-32 borrow
+// deferred, all on the ALU pipe or with one IMAD.WIDE, and the carry fix-up moved to the multiplier pipe -- equal or slower.)
+GL_HD gl_t gl_reduce128_defer(gl_t lo, gl_t hi, uint32_t &bf)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 p0,p1,p2,p3,m;\n\t"
+        "mov.b64 {p0,p1}, %2;\n\t"
+        "mov.b64 {p2,p3}, %3;\n\t"
+        "sub.cc.u32 p0, p0, p3;\n\t"
+        "subc.cc.u32 p1, p1, 0;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"                     // bf -= borrow
+        GL_PTX_ADD_EPS_MUL_FMA("p0", "p1", "p2")
+        "addc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        "add.u32 p1, p1, m;\n\t"
+        "mov.b64 %0, {p0,p1};\n\t"
+        "}" : "=l"(r), "+r"(bf) : "l"(lo), "l"(hi));
+    return r;
+#else
+    (void)bf;
+    return gl_reduce128_t<false>(lo, hi);
+#endif
+}
+
 // MODE 0: p2*EPS as IMAD.LO + IMAD.HI; 1: on the ALU pipe; 2: one IMAD.WIDE (gl_reduce128_wide)
 template <int MODE>
 GL_HD gl_t gl_reduce128_m(gl_t lo, gl_t hi)
@@ -360,6 +391,20 @@ GL_HD gl_t gl_pow7_m(gl_t x)
     gl_t x3 = gl_mul_m<MODE, W4>(x, x2);
     gl_t x4 = gl_sqr_m<MODE>(x2);
     return gl_mul_m<MODE, W4>(x3, x4);
+}
+
+// the same with the rare wrap of every fold deferred into bf (gl_reduce128_defer)
+GL_HD gl_t gl_pow7_defer(gl_t x, uint32_t &bf)
+{
+    gl_t lo, hi;
+    gl_sqr_wide(x, lo, hi);
+    const gl_t x2 = gl_reduce128_defer(lo, hi, bf);
+    gl_mul_wide(x, x2, lo, hi);
+    const gl_t x3 = gl_reduce128_defer(lo, hi, bf);
+    gl_sqr_wide(x2, lo, hi);
+    const gl_t x4 = gl_reduce128_defer(lo, hi, bf);
+    gl_mul_wide(x3, x4, lo, hi);
+    return gl_reduce128_defer(lo, hi, bf);
 }
 
 // x^7, the Poseidon S-box (poseidon_goldilocks.hpp:91-97): 4 multiplies

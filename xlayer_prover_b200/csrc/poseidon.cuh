@@ -99,7 +99,20 @@ GL_HD void gl_dot_mac(GlDotAcc &s, gl_t a, gl_t b)
 #ifndef POS_FOLD_MODE
 #define POS_FOLD_MODE (POS_EPS_ALU_FOLD ? 1 : 0)
 #endif
-GL_HD gl_t pos_pow7(gl_t x) { return gl_pow7_m<POS_RED_MODE, POS_MUL4W != 0>(x); }
+// DEFER (the leaf hash, POS_DEFER_BORROW): every fold leaves its 2^-33 wrap uncorrected and counts it in bf instead
+// (gl_reduce128_defer); the caller redoes the row with DEFER = false when bf != 0 at the end.
+template <bool DEFER>
+GL_HD gl_t pos_pow7(gl_t x, uint32_t &bf)
+{
+    if (DEFER) return gl_pow7_defer(x, bf);
+    return gl_pow7_m<POS_RED_MODE, POS_MUL4W != 0>(x);
+}
+template <bool DEFER, int MODE>
+GL_HD gl_t pos_fold128(gl_t lo, gl_t hi, uint32_t &bf)
+{
+    if (DEFER) return gl_reduce128_defer(lo, hi, bf);
+    return gl_reduce128_m<MODE>(lo, hi);
+}
 
 #ifndef POS_EPS_ALU_FOLD
 #define POS_EPS_ALU_FOLD 0        // 1: the p2*EPS term of the dot-product folds on the ALU pipe (experiment)
@@ -109,7 +122,8 @@ GL_HD gl_t pos_pow7(gl_t x) { return gl_pow7_m<POS_RED_MODE, POS_MUL4W != 0>(x);
 #endif
 // value = Z + X*2^32 + Y*2^64  ->  limbs l0..l4 (weights 2^0..2^128), then
 //   (l1:l0) + l2*EPS - l3 - l4*2^32   (2^64 = EPS, 2^96 = -1, 2^128 = -2^32)
-GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
+template <bool DEFER>
+GL_HD gl_t gl_dot_fold(const GlDotAcc &s, uint32_t &bf)
 {
     uint64_t t1 = (uint64_t)s.z1 + s.x0;
     uint64_t t2 = (uint64_t)s.zc + s.x1 + s.y0 + (t1 >> 32);
@@ -117,12 +131,13 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s)
     uint64_t l4 = (uint64_t)s.yc + (t3 >> 32);
     gl_t lo = ((t1 & 0xFFFFFFFFULL) << 32) | s.z0;
     gl_t hi = ((t3 & 0xFFFFFFFFULL) << 32) | (t2 & 0xFFFFFFFFULL);
-    gl_t r = gl_reduce128_m<POS_FOLD_MODE>(lo, hi);
+    gl_t r = pos_fold128<DEFER, POS_FOLD_MODE>(lo, hi, bf);
     return gl_sub(r, l4 << 32);
 }
 
 // a*b + c, one fold (c is added into the 128-bit product: (2^64-1)^2 + 2^64 - 1 < 2^128)
-GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c)
+template <bool DEFER>
+GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c, uint32_t &bf)
 {
     gl_t lo, hi;
     if (POS_MUL4W) gl_mul_wide4(a, b, lo, hi);
@@ -134,7 +149,7 @@ GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c)
     hi += (t < lo);
     lo = t;
 #endif
-    return gl_reduce128_m<POS_MULADD_MODE>(lo, hi);
+    return pos_fold128<DEFER, POS_MULADD_MODE>(lo, hi, bf);
 }
 
 // ---- MDS layer: state' = M^T state,  M[j][i] = circ[(j-i) mod 12] (+8 at i=j=0) ----
@@ -323,25 +338,26 @@ GL_HD void pos_round_sync()
 
 // x_i = x_i^7 + rc_i for all 12, as 12/G trips over G lanes with the state rotated by G after each trip
 // (rc == NULL: no constant here, it was folded into the linear layer that follows -- POS_MDS_LIMB)
-GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc)
+template <bool DEFER>
+GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc, uint32_t &bf)
 {
     constexpr int G = POS_SBOX_GROUP;
     static_assert(12 % G == 0, "POS_SBOX_GROUP must divide 12");
     if (!rc) {
 #pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = pos_pow7(x[i]);
+        for (int i = 0; i < 12; i++) x[i] = pos_pow7<DEFER>(x[i], bf);
         return;
     }
     if (G == 12) {
 #pragma unroll
-        for (int i = 0; i < 12; i++) x[i] = gl_add_c(pos_pow7(x[i]), rc[i]);
+        for (int i = 0; i < 12; i++) x[i] = gl_add_c(pos_pow7<DEFER>(x[i], bf), rc[i]);
         return;
     }
 #pragma unroll 1
     for (int q = 0; q < 12 / G; q++) {
         gl_t t[G];
 #pragma unroll
-        for (int i = 0; i < G; i++) t[i] = gl_add_c(pos_pow7(x[i]), rc[q * G + i]);
+        for (int i = 0; i < G; i++) t[i] = gl_add_c(pos_pow7<DEFER>(x[i], bf), rc[q * G + i]);
 #pragma unroll
         for (int i = 0; i + G < 12; i++) x[i] = x[i + G];
 #pragma unroll
@@ -350,7 +366,8 @@ GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc)
 }
 
 // x <- PRE^T x  (the dense pre-multiplied matrix before the partial rounds)
-GL_HD void pos_pre_layer(gl_t x[12])
+template <bool DEFER>
+GL_HD void pos_pre_layer(gl_t x[12], uint32_t &bf)
 {
 #if POS_ROLL_PRE
     gl_t out[12];
@@ -369,7 +386,7 @@ GL_HD void pos_pre_layer(gl_t x[12])
         for (int j = 0; j < 12; j++) gl_dot_mac(acc, x[j], col[j]);
 #pragma unroll
         for (int k = 0; k < 11; k++) out[k] = out[k + 1];
-        out[11] = gl_dot_fold(acc);
+        out[11] = gl_dot_fold<DEFER>(acc, bf);
     }
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = out[i];
@@ -387,13 +404,13 @@ GL_HD void pos_pre_layer(gl_t x[12])
 #endif
 #pragma unroll
         for (int j = 0; j < 12; j++) gl_dot_mac(acc, y[j], POS_PRE[j * 12 + i]);
-        x[i] = gl_dot_fold(acc);
+        x[i] = gl_dot_fold<DEFER>(acc, bf);
     }
 #endif
 }
 
-template <bool LOCKSTEP>
-GL_HD void pos_permute_t(gl_t x[12])
+template <bool LOCKSTEP, bool DEFER>
+GL_HD void pos_permute_t(gl_t x[12], uint32_t &bf)
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = gl_add_c(x[i], POS_RC[i]);
@@ -404,7 +421,7 @@ GL_HD void pos_permute_t(gl_t x[12])
     for (int r = 0; r < 8; r++) {
         pos_round_sync<LOCKSTEP>();
 #if POS_MDS_LIMB
-        pos_sbox_layer(x, nullptr);                      // constants ride in the linear layer's accumulators
+        pos_sbox_layer<DEFER>(x, nullptr, bf);                      // constants ride in the linear layer's accumulators
         if (r != 3) {
 #if POS_MDS_LIMB == 2
             pos_mds_f64(x, POS_MRCD + 24 * r);
@@ -413,28 +430,32 @@ GL_HD void pos_permute_t(gl_t x[12])
 #endif
         } else {
 #else
-        pos_sbox_layer(x, POS_RCF + 12 * r);
+        pos_sbox_layer<DEFER>(x, POS_RCF + 12 * r, bf);
         if (r != 3) {
             pos_mds(x);
         } else {
 #endif
-            pos_pre_layer(x);
+            pos_pre_layer<DEFER>(x, bf);
             // partial rounds: x0 = x0^7 + C;  s0 = <x, S[0..12)>;  x_i += x0 * S[11+i] (i >= 1);  x0 = s0
 #pragma unroll 1
             for (int p = 0; p < 22; p++) {
                 pos_round_sync<LOCKSTEP>();
                 const gl_t *S = POS_SP + 23 * p;
-                x[0] = gl_add_c(pos_pow7(x[0]), POS_RC[60 + p]);
+                x[0] = gl_add_c(pos_pow7<DEFER>(x[0], bf), POS_RC[60 + p]);
                 GlDotAcc acc;
                 gl_dot_init(acc);
 #pragma unroll
                 for (int i = 0; i < 12; i++) gl_dot_mac(acc, x[i], S[i]);
 #pragma unroll
-                for (int i = 1; i < 12; i++) x[i] = gl_mul_add(x[0], S[11 + i], x[i]);
-                x[0] = gl_dot_fold(acc);
+                for (int i = 1; i < 12; i++) x[i] = gl_mul_add<DEFER>(x[0], S[11 + i], x[i], bf);
+                x[0] = gl_dot_fold<DEFER>(acc, bf);
             }
         }
     }
 }
 
-GL_HD void pos_permute(gl_t x[12]) { pos_permute_t<false>(x); }
+GL_HD void pos_permute(gl_t x[12])
+{
+    uint32_t bf = 0;
+    pos_permute_t<false, false>(x, bf);
+}

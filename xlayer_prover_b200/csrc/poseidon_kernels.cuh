@@ -53,11 +53,58 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 #else
 #define POS_LEAF_BOUNDS __launch_bounds__(POS_LEAF_BLOCK)
 #endif
+// POS_DEFER_BORROW: the row is hashed with the folds' rare wrap deferred (gl_reduce128_defer: two ALU instructions fewer
+// in each of the 748 folds of a permutation); a row in which any fold did wrap (2^-33 per fold: about one row in 10^4 at
+// 83 permutations a row) is hashed again by pos_leaf_row_exact, a separate out-of-line copy with the exact folds.
+// g_pos_redo_rows counts those rows (glp_leaf_redo_rows; the GPU tests drive crafted rows through it).
+#ifndef POS_DEFER_BORROW
+#define POS_DEFER_BORROW 1
+#endif
+#if !defined(GLP_EMU)
+static __device__ unsigned long long g_pos_redo_rows;
+#endif
+
+// the sponge over one row; returns the deferred-wrap count (always 0 when !DEFER)
+template <bool LOCKSTEP, bool DEFER>
+static __device__ __forceinline__ uint32_t pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap)
+{
+    gl_t nxt[8];
+    uint32_t bf = 0;
+    const uint64_t nblk = (ncols + 7) / 8;
+    pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16);
+#pragma unroll
+    for (int i = 8; i < 12; i++) x[i] = cap ? cap[i - 8] : 0;   // capacity starts at zero (:243-246)
+#pragma unroll 1
+    for (uint64_t b = 0; b < nblk; b++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) x[i] = nxt[i];
+        if (b + 1 < nblk) {                        // prefetch the next 64 bytes of this row under the permutation
+            uint64_t rem = ncols - 8 * (b + 1);
+            pos_load8(nxt, p + 8 * (b + 1), (uint32_t)(rem < 8 ? rem : 8), vec16);
+        }
+        pos_permute_t<LOCKSTEP, DEFER>(x, bf);
+#pragma unroll
+        for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
+    }
+    return bf;
+}
+static __device__ GLP_NOINLINE void pos_leaf_row_exact(gl_t *o, const gl_t *p, uint64_t ncols, int vec16, const gl_t *cap)
+{
+    gl_t x[12];
+    pos_leaf_row<false, false>(x, p, ncols, vec16 != 0, cap);
+#pragma unroll
+    for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
+#if !defined(GLP_EMU)
+    atomicAdd(&g_pos_redo_rows, 1ull);
+#endif
+}
+
 template <bool LOCKSTEP>
 __global__ void POS_LEAF_BOUNDS
 k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in,
                    uint64_t out_pitch)
 {
+    constexpr bool DEFER = POS_DEFER_BORROW && !LOCKSTEP;     // a redone row would miss the other warps' barriers
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = row < nrows;
     if (!live) {
@@ -73,23 +120,12 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
         }
         return;
     }
+    const gl_t *cap = cap_in ? cap_in + row * out_pitch : nullptr;
     gl_t x[12];
-    gl_t nxt[8];
-    uint64_t nblk = (ncols + 7) / 8;
-    pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16 != 0);
-#pragma unroll
-    for (int i = 8; i < 12; i++) x[i] = cap_in ? cap_in[row * out_pitch + (i - 8)] : 0;   // capacity starts at zero (:243-246)
-#pragma unroll 1
-    for (uint64_t b = 0; b < nblk; b++) {
-#pragma unroll
-        for (int i = 0; i < 8; i++) x[i] = nxt[i];
-        if (b + 1 < nblk) {                        // prefetch the next 64 bytes of this row under the permutation
-            uint64_t rem = ncols - 8 * (b + 1);
-            pos_load8(nxt, p + 8 * (b + 1), (uint32_t)(rem < 8 ? rem : 8), vec16 != 0);
-        }
-        pos_permute_t<LOCKSTEP>(x);
-#pragma unroll
-        for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
+    const uint32_t bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap);
+    if (DEFER && bf) {                            // before any store: cap_in may alias out
+        pos_leaf_row_exact(o, p, ncols, vec16, cap);
+        return;
     }
     if (live) {
 #pragma unroll
