@@ -429,19 +429,69 @@ GL_HD gl_t gl_pow(gl_t b, uint64_t e)
 
 GL_HD gl_t gl_inv(gl_t a) { return gl_pow(a, GL_P - 2); }
 
+// lo + h*EPS for h < 2^32 (the fold of a value below 2^96: its p3 is zero, so the "- p3" half of gl_reduce128 drops out)
+GL_HD gl_t gl_fold96(gl_t lo, uint32_t h)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 p0,p1,m;\n\t"
+        "mov.b64 {p0,p1}, %1;\n\t"
+        GL_PTX_ADD_EPS_MUL_FMA("p0", "p1", "%2")
+        "addc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        "add.u32 p1, p1, m;\n\t"
+        "mov.b64 %0, {p0,p1};\n\t"
+        "}" : "=l"(r) : "l"(lo), "r"(h));
+    return r;
+#else
+    const gl_t t = ((gl_t)h << 32) - h;
+    gl_t r = lo + t;
+    if (r < t) r += GL_EPS;
+    return r;
+#endif
+}
+// w0*EPS - w1 - w2*2^32  ( = (w0 + w1*2^32 + w2*2^64) * 2^64 mod p ) for w2 < 2^31.  w0*EPS <= (2^32-1)^2 and the
+// subtrahend (w2:w1) is below 2^63, so one conditional wrap is exact.
+GL_HD gl_t gl_fold_times_2p64(uint32_t w0, uint32_t w1, uint32_t w2)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 r0,r1,m;\n\t"
+        "sub.cc.u32 r0, 0, %1;\n\t"                   // (w0 << 32) - w0
+        "subc.u32 r1, %1, 0;\n\t"
+        "sub.cc.u32 r0, r0, %2;\n\t"
+        "subc.cc.u32 r1, r1, %3;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                       // 0xffffffff on borrow
+        "sub.cc.u32 r0, r0, m;\n\t"                   // - EPS on borrow
+        "subc.u32 r1, r1, 0;\n\t"
+        "mov.b64 %0, {r0,r1};\n\t"
+        "}" : "=l"(r) : "r"(w0), "r"(w1), "r"(w2));
+    return r;
+#else
+    const gl_t x = ((gl_t)w0 << 32) - w0, y = ((gl_t)w2 << 32) | w1;
+    gl_t r = x - y;
+    if (x < y) r -= GL_EPS;
+    return r;
+#endif
+}
+
 // a * 2^k (mod p) for 0 <= k < 96: shifts and one fold, no multiplier.  Because W[6] = 8 every twiddle
-// of a 64-point (and so of a 16-point) transform is such a power of two.
+// of a 64-point (and so of a 16-point) transform is such a power of two.  k is a compile-time constant at every call
+// site of the NTT kernels, so only one of the branches survives:
+//   k <= 32      : a*2^k < 2^96                    -> gl_fold96                    (9 instructions with the shifts)
+//   32 < k <= 64 : the general fold                                               (15)
+//   k > 64       : (a * 2^(k-64)) * 2^64, 95 bits  -> gl_fold_times_2p64           (10; was 18)
 GL_HD gl_t gl_mul_pow2(gl_t a, unsigned k)
 {
-    // a * 2^k = v0 + v1*2^64 + v2*2^128 with v2*2^128 = v2 * 2^96 * 2^32 = -(v2 << 32)
-    gl_t v0, v1, v2;
     if (k == 0) return a;
-    if (k < 64) { v0 = a << k; v1 = a >> (64 - k); v2 = 0; }
-    else if (k == 64) { v0 = 0; v1 = a; v2 = 0; }
-    else { v0 = 0; v1 = a << (k - 64); v2 = a >> (128 - k); }
-    gl_t r = gl_reduce128(v0, v1);
-    if (k > 64) r = gl_sub(r, v2 << 32);     // v2 < 2^32
-    return r;
+    if (k <= 32) return gl_fold96(a << k, (uint32_t)(a >> (64 - k)));
+    if (k < 64) return gl_reduce128(a << k, a >> (64 - k));
+    if (k == 64) return gl_reduce128(0, a);
+    const gl_t w = a << (k - 64);
+    return gl_fold_times_2p64((uint32_t)w, (uint32_t)(w >> 32), (uint32_t)(a >> (128 - k)));
 }
 
 // primitive 2^k-th root of unity, the reference's Goldilocks::w(k)
