@@ -35,7 +35,12 @@
 
 #define NTT_MAX_LOGQ 8              // tile rows <= 2^8
 #define NTT_LOGT 12                 // two-level tables: low 12 bits / the rest
+#ifndef NTT_WARPS
 #define NTT_WARPS 16
+#endif
+#ifndef NTT_MINBLOCKS
+#define NTT_MINBLOCKS 2              // CTAs per SM the register allocation is capped for (16 warps x 2: 64 registers)
+#endif
 #define NTT_LANES 32
 #define NTT_THREADS (NTT_WARPS * NTT_LANES)
 #define NTT_MAX_PASSES 4
@@ -300,7 +305,7 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
 }
 
 template <int A, int B, bool INV, int LSH, bool NARROW>
-__global__ void __launch_bounds__(NTT_THREADS, 2)
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINBLOCKS)
 k_ntt_pass(NttPass a)
 {
     GLP_DYN_SMEM(gl_t, tile);                                    // [Q][32] when B > 0
