@@ -49,6 +49,9 @@ uint64_t glp_launch_count(const glp_ctx *ctx);
 /* leaf rows the hash kernel has had to redo with its exact arithmetic since the library was loaded (the fast path leaves a
  * 2^-33-per-multiplication wrap uncorrected and detects it); synchronises the context.  Diagnostics only. */
 uint64_t glp_leaf_redo_rows(glp_ctx *ctx);
+/* low-degree extensions this context has had to repeat with the exact NTT passes after the optimistic ones flagged a
+ * left-out wrap (2^-64 per butterfly on honest data).  Diagnostics only. */
+uint64_t glp_ntt_retry_count(const glp_ctx *ctx);
 /* cap on internal scratch in bytes (0 = default: a quarter of free device memory, at most 16 GiB) */
 int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes);
 
@@ -82,9 +85,10 @@ int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_pitch, cons
  * parts[i / R] + (i % R) * part_pitch + part_col0, R = n_ext / nparts (nparts a power of two).  This is the multi-GPU
  * exchange of SURVEY 8e fused into the transform: rank g passes the row slabs of all ranks (its own, and its peers'
  * mapped with glp_ipc_import), part_col0 = its first column, and the last NTT pass stores every tile straight into the
- * owner's reference-layout [R x part_pitch] slab over NVLink -- no all-to-all, no re-interleave pass.  Asynchronous on
- * the context's stream when `in` is a device pointer; a host `in` is uploaded column block by column block under the
- * transform of the previous block and the call returns when everything has been stored.  `parts` is a host array. */
+ * owner's reference-layout [R x part_pitch] slab over NVLink -- no all-to-all, no re-interleave pass.  A host `in` is
+ * uploaded column block by column block under the transform of the previous block; a device `in` must not overlap any
+ * slab (the transform may be issued twice, see glp_ntt_retry_count).  Either way the call returns when this rank's
+ * stores have been issued and its stream is idle; the caller still fences the peers.  `parts` is a host array. */
 int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint32_t nparts, uint64_t part_pitch, uint64_t part_col0,
                            const uint64_t *in, uint64_t in_pitch, uint64_t n_ext, uint64_t n, uint64_t ncols);
 /* CUDA IPC plumbing for the above (one process per GPU): export a glp_device_alloc'ed buffer as 64 opaque bytes,

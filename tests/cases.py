@@ -165,6 +165,53 @@ def check_commit(ctx, oracle, a, n_ext, **kw):
     check_equal(root, want_tree[-4:], "commit root")
 
 
+def wrap_twice_matrix(rng, n, ncols):
+    """Inputs that make the butterflies of the INTT's first two stages wrap TWICE: with rows r, r + n/4, r + n/2, r + 3n/4
+    of a column set to (p-1, p-1, 2^32-1, 2^32-1) stage 1 leaves 2^64-1 in two registers (no carry, legal but >= p) and
+    stage 2 adds them (second carry); with (0, p-1, 0, 2^32-1) stage 2 subtracts 2^64-1 from 0 (second borrow).  The
+    optimistic NTT passes (k_ntt_pass_opt) leave those wraps out, flag them, and the LDE is repeated exactly."""
+    a = rng.integers(0, P, size=(n, ncols), dtype=np.uint64)
+    q = n // 4
+    a[1, 0], a[1 + q, 0], a[1 + 2 * q, 0], a[1 + 3 * q, 0] = P - 1, P - 1, 2 ** 32 - 1, 2 ** 32 - 1
+    c = ncols - 1
+    a[q - 1, c], a[2 * q - 1, c], a[3 * q - 1, c], a[4 * q - 1, c] = 0, P - 1, 0, 2 ** 32 - 1
+    return a
+
+
+def check_optimistic_lde(make_ctx, oracle, rng, n=256, ncols=20):
+    """device-resident extendPol / commit: exact results whether or not the optimistic passes had to be repeated.
+    make_ctx(**env) -> a fresh context created under those environment variables; ncols > 16 (narrower matrices take the
+    NARROW lane mapping, which has no optimistic flavour)"""
+    n_ext = 2 * n
+    honest = rng.integers(0, P, size=(n, ncols), dtype=np.uint64)
+    crafted = wrap_twice_matrix(rng, n, ncols)
+    ctx = make_ctx()
+    try:
+        r0 = ctx.ntt_retry_count()
+        check_equal(run_extend(ctx, honest, n_ext, device=True), oracle.extend_pol(honest, n_ext), "optimistic LDE, honest data")
+        assert ctx.ntt_retry_count() == r0, "honest data must not need the exact passes"
+        check_equal(run_extend(ctx, crafted, n_ext, device=True), oracle.extend_pol(crafted, n_ext), "optimistic LDE, crafted data")
+        assert ctx.ntt_retry_count() == r0 + 1, "crafted data must have been repeated with the exact passes"
+        check_commit(ctx, oracle, crafted, n_ext, device=True)
+        assert ctx.ntt_retry_count() == r0 + 2
+        check_equal(run_extend(ctx, crafted, n_ext, device=True, alias=True), oracle.extend_pol(crafted, n_ext), "in place: exact passes directly")
+        assert ctx.ntt_retry_count() == r0 + 2
+    finally:
+        ctx.close()
+    ctx = make_ctx(GLP_NTT_FORCE_RETRY=1)
+    try:
+        check_equal(run_extend(ctx, honest, n_ext, device=True), oracle.extend_pol(honest, n_ext), "forced retry")
+        assert ctx.ntt_retry_count() == 1
+    finally:
+        ctx.close()
+    ctx = make_ctx(GLP_NTT_OPT=0)
+    try:
+        check_equal(run_extend(ctx, crafted, n_ext, device=True), oracle.extend_pol(crafted, n_ext), "optimistic passes off")
+        assert ctx.ntt_retry_count() == 0
+    finally:
+        ctx.close()
+
+
 # ---- the callers either side of the commit (SURVEY 8f N1, N3, N4); the oracle is the reference build ----
 def check_quotient_commit(ctx, reference, rng, shapes=((16, 2, 3, 2), (64, 4, 3, 2), (32, 8, 3, 4), (128, 2, 1, 2))):
     """Starks::genProof step 4 (starks.cpp:261-291): (n, blowup, qDim, qDeg) -> cm4 and every Merkle node."""

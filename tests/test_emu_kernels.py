@@ -90,6 +90,26 @@ def test_merkletree_batch(ectx, oracle, golden, rng):
     check_merkletree_batch(ectx, oracle, golden, rng)
 
 
+def test_optimistic_lde(emu_lib, oracle, rng):
+    """the optimistic passes' flag / host retry logic (the emulator's gl_add_defer / gl_sub_defer really leave the wrap out)"""
+    from cases import check_optimistic_lde
+    from xlayer_prover_b200._capi import Context
+
+    def make(**env):
+        old = {k: os.environ.get(k) for k in env}
+        os.environ.update({k: str(v) for k, v in env.items()})
+        try:
+            return Context(0, emu_lib)
+        finally:
+            for k, v in old.items():
+                if v is None:
+                    os.environ.pop(k, None)
+                else:
+                    os.environ[k] = v
+    check_optimistic_lde(make, oracle, rng, n=128, ncols=34)       # one 2^7-row tile pass down, one 2^8-row pass up
+    check_optimistic_lde(make, oracle, rng, n=2048, ncols=17)      # 6-bit tiles: (6, 5) down, (6, 6) up
+
+
 def test_ntt_single_pass(ectx, oracle, fixtures, rng):
     for n, c in [(1, 3), (2, 3), (4, 1), (16, 8), (32, 5), (128, 2)]:
         check_ntt(ectx, oracle, edge_matrix(rng, n, c))

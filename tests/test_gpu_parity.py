@@ -115,6 +115,14 @@ def test_linear_hash_deferred_wrap_rows_are_redone(ctx, oracle, rng):
     assert ctx.leaf_redo_rows() - before >= 3 * len(crafted)
 
 
+def test_optimistic_lde_is_repeated_exactly_when_flagged(oracle, rng):
+    """k_ntt_pass_opt + dev_extend_pol_checked: crafted inputs fire the left-out wraps, the LDE is repeated with the exact
+    passes; sizes with one, two and three tile passes"""
+    from cases import check_optimistic_lde
+    for n, ncols in ((128, 33), (1 << 13, 40), (1 << 15, 20), (1 << 17, 17)):
+        check_optimistic_lde(env_ctx, oracle, rng, n=n, ncols=ncols)
+
+
 def test_merkletree_kats(ctx, golden):
     check_equal(run_merkletree(ctx, fib_matrix(64, 128))[-4:], golden["merkletree_64x128_root"]["out"], "64x128")
     check_equal(run_merkletree(ctx, fib_matrix(64, 128), device=True)[-4:], golden["merkletree_64x128_root"]["out"], "64x128 dev")

@@ -27,6 +27,7 @@ SIGNATURES = {
     "glp_synchronize": (i32, [vp]),
     "glp_launch_count": (u64, [vp]),
     "glp_leaf_redo_rows": (u64, [vp]),
+    "glp_ntt_retry_count": (u64, [vp]),
     "glp_set_scratch_limit": (i32, [vp, u64]),
     "glp_device_alloc": (i32, [vp, u64, C.POINTER(vp)]),
     "glp_device_free": (i32, [vp, vp]),
@@ -150,6 +151,7 @@ class Context:
     def synchronize(self): self.lib.check(self.lib.glp_synchronize(self.h))
     def launch_count(self): return self.lib.glp_launch_count(self.h)
     def leaf_redo_rows(self): return int(self.lib.glp_leaf_redo_rows(self.h))
+    def ntt_retry_count(self): return int(self.lib.glp_ntt_retry_count(self.h))
     def set_scratch_limit(self, nbytes): self.lib.check(self.lib.glp_set_scratch_limit(self.h, nbytes))
 
     def device_alloc(self, nbytes):

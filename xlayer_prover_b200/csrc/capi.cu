@@ -64,6 +64,14 @@ struct glp_ctx {
     uint64_t merkle_stream_min = 0;          // GLP_MERKLE_STREAM_MIN: bytes from which a host-resident Merkle source is uploaded block by block (tests lower it)
     bool stage_all = true;                   // GLP_STAGE_ALL=0: two alternating upload buffers even when the whole input fits
     bool no_narrow = false;                  // GLP_NTT_NO_NARROW=1: lane = column even for matrices of <= 16 columns (comparison runs)
+    // optimistic NTT passes (k_ntt_pass_opt): the device-resident LDE runs them and is repeated with the exact passes when
+    // the flag they raise is set (dev_extend_pol_checked)
+    bool opt_enabled = true;                 // GLP_NTT_OPT=0 turns them off
+    bool opt_active = false;                 // true while dev_extend_pol_checked issues its first attempt
+    bool opt_force_retry = false;            // GLP_NTT_FORCE_RETRY=1 (tests): behave as if the flag had been raised
+    uint32_t *opt_flag_dev = nullptr;        // device word the kernels write
+    uint32_t *opt_flag_host = nullptr;       // pinned copy
+    uint64_t opt_retries = 0;                // transforms repeated with the exact passes (glp_ntt_retry_count)
     bool no_fused_lde = false;               // GLP_NTT_NO_FUSED_LDE=1: extendPol as two natural-order transforms (the fallback path)
     std::map<uint32_t, TwoLevel> tw_tabs;    // w_N^e, by logN
     std::map<uint32_t, TwoLevel> sc_tabs;    // shift^j / N, by logN
@@ -176,6 +184,10 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_fused_lde = nfl && atoi(nfl) != 0;
     const char *nn = getenv("GLP_NTT_NO_NARROW");
     ctx->no_narrow = nn && atoi(nn) != 0;
+    const char *no = getenv("GLP_NTT_OPT");
+    if (no) ctx->opt_enabled = atoi(no) != 0;
+    const char *nfr = getenv("GLP_NTT_FORCE_RETRY");
+    ctx->opt_force_retry = nfr && atoi(nfr) != 0;
     const char *tr = getenv("GLP_TRACE");
     ctx->trace = tr && atoi(tr) != 0;
     const char *msm = getenv("GLP_MERKLE_STREAM_MIN");
@@ -194,6 +206,8 @@ extern "C" void glp_destroy(glp_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (void *p : ctx->tables) cudaFree(p);
+    if (ctx->opt_flag_dev) cudaFree(ctx->opt_flag_dev);
+    if (ctx->opt_flag_host) cudaFreeHost(ctx->opt_flag_host);
     release(ctx->s1); release(ctx->s2); release(ctx->ext); release(ctx->nodes);
     release(ctx->tmp_in); release(ctx->tmp_out); release(ctx->partial); release(ctx->work); release(ctx->parts_tab);
     cudaStreamDestroy(ctx->own_stream);
@@ -216,6 +230,7 @@ extern "C" int glp_synchronize(glp_ctx *ctx)
     return GLP_OK;
 }
 extern "C" uint64_t glp_launch_count(const glp_ctx *ctx) { return ctx ? ctx->launches : 0; }
+extern "C" uint64_t glp_ntt_retry_count(const glp_ctx *ctx) { return ctx ? ctx->opt_retries : 0; }
 extern "C" uint64_t glp_leaf_redo_rows(glp_ctx *ctx)
 {
     unsigned long long n = 0;
@@ -455,10 +470,20 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t 
             LAUNCH(ctx, kfn, (unsigned)(grid < cog ? grid : cog), ctx->co_threads, smem, a, (uint32_t)grid); \
         }                                                                            \
     } while (0)
+#define NTT_GO_OPT(INV, LSH)                                                         \
+    do {                                                                             \
+        if constexpr (B > 0 && A + B >= 6) {                                         \
+            auto kfn = k_ntt_pass_opt<A, B, INV, LSH>;                               \
+            if (smem > 48 * 1024) GLP_SET_SMEM(kfn, smem);                           \
+            a.defer_flag = ctx->opt_flag_dev;                                        \
+            LAUNCH(ctx, kfn, (unsigned)grid, NTT_THREADS, smem, a);                  \
+        }                                                                            \
+    } while (0)
 #define NTT_GO(INV, LSH)                                                             \
     do {                                                                             \
         if (narrow) NTT_GO2(INV, LSH, true);                                         \
         else if (B > 0 && A + B >= 7 && ctx->co_active) NTT_GO_CO(INV, LSH);         \
+        else if (B > 0 && A + B >= 6 && ctx->opt_active) NTT_GO_OPT(INV, LSH);       \
         else NTT_GO2(INV, LSH, false);                                               \
     } while (0)
     if (inv) NTT_GO(true, 0);
@@ -468,6 +493,7 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t 
     else NTT_GO(false, 0);
 #undef NTT_GO
 #undef NTT_GO_CO
+#undef NTT_GO_OPT
 #undef NTT_GO2
     return GLP_OK;
 }
@@ -739,6 +765,45 @@ static int dev_extend_pol(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_
     return GLP_OK;
 }
 
+// Optimistic execution of a device-resident LDE: `issue` enqueues the whole transform on ctx->stream.  It is enqueued first
+// with the passes whose butterflies leave out the second wrap of every add / subtract (k_ntt_pass_opt; the wrap fires with
+// probability 2^-64 per operation on honest data), and -- only if one of them raised the flag, which the host reads after a
+// stream synchronise -- once more with the exact passes.  The input must survive the first attempt (`rerunnable`: no
+// overlap between input and output), otherwise the exact passes run directly.  Returns with the stream idle.
+template <class F>
+static int with_optimistic_ntt(glp_ctx *ctx, bool rerunnable, F &&issue)
+{
+    if (!ctx->opt_enabled || !rerunnable || ctx->no_fused_lde) {
+        GLP(issue());
+        CU(cudaStreamSynchronize(ctx->stream));
+        return GLP_OK;
+    }
+    if (!ctx->opt_flag_dev) {
+        CU(cudaMalloc((void **)&ctx->opt_flag_dev, sizeof(uint32_t)));
+        CU(cudaHostAlloc((void **)&ctx->opt_flag_host, sizeof(uint32_t), cudaHostAllocDefault));
+    }
+    CU(cudaMemsetAsync(ctx->opt_flag_dev, 0, sizeof(uint32_t), ctx->stream));
+    ctx->opt_active = true;
+    const int rc = issue();
+    ctx->opt_active = false;
+    if (rc != GLP_OK) return rc;
+    CU(cudaMemcpyAsync(ctx->opt_flag_host, ctx->opt_flag_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (*ctx->opt_flag_host || ctx->opt_force_retry) {
+        ctx->opt_retries++;
+        GLP(issue());
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    return GLP_OK;
+}
+static int dev_extend_pol_checked(glp_ctx *ctx, gl_t *out, uint64_t out_pitch, const gl_t *in, uint64_t in_pitch, uint64_t n_ext, uint64_t n,
+                                  uint64_t ncols)
+{
+    const gl_t *in_end = in + (n - 1) * in_pitch + ncols, *out_end = out + (n_ext - 1) * out_pitch + ncols;
+    return with_optimistic_ntt(ctx, in_end <= out || out_end <= in,
+                               [&]() -> int { return dev_extend_pol(ctx, out, out_pitch, in, in_pitch, n_ext, n, ncols); });
+}
+
 // ------------------------------------------------------------------------------------------------
 // host <-> device staging helpers
 // ------------------------------------------------------------------------------------------------
@@ -887,14 +952,17 @@ extern "C" int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint
         CU(e0); CU(e1);
         return GLP_OK;
     }
+    // device input (which must not overlap any slab): optimistic passes, repeated exactly if they flag; returns synchronised
     const uint32_t wb = pick_block_cols(ctx, n + n_ext, ncols);
     GLP(ensure(ctx, ctx->work, (size_t)n_ext * wb * sizeof(gl_t)));
-    for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
-        const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-        sc.col0 = part_col0 + c0;
-        GLP(lde_block(ctx, logN, logE, (const gl_t *)in + c0, in_pitch, (gl_t *)ctx->work.p, w, w, &sc));
-    }
-    return GLP_OK;
+    return with_optimistic_ntt(ctx, true, [&]() -> int {
+        for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
+            const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
+            sc.col0 = part_col0 + c0;
+            GLP(lde_block(ctx, logN, logE, (const gl_t *)in + c0, in_pitch, (gl_t *)ctx->work.p, w, w, &sc));
+        }
+        return GLP_OK;
+    });
 }
 
 extern "C" int glp_ipc_export(glp_ctx *ctx, void *devptr, unsigned char handle[64])
@@ -931,9 +999,7 @@ extern "C" int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, u
     CU(cudaSetDevice(ctx->device));
     const bool in_dev = on_device(in), out_dev = on_device(out);
     if (in_dev && out_dev) {
-        GLP(dev_extend_pol(ctx, (gl_t *)out, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
-        CU(cudaStreamSynchronize(ctx->stream));
-        return GLP_OK;
+        return dev_extend_pol_checked(ctx, (gl_t *)out, ncols, (const gl_t *)in, ncols, n_ext, n, ncols);
     }
     return glp_commit(ctx, out, nullptr, nullptr, in, n, n_ext, ncols);
 }
@@ -1424,7 +1490,7 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
         GLP(commit_overlapped(ctx, dext, dtree, (const gl_t *)in, n, n_ext, ncols));
         if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     } else {
-        GLP(dev_extend_pol(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
+        GLP(dev_extend_pol_checked(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
         if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
         if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
     }

@@ -141,6 +141,65 @@ GL_HD gl_t gl_sub(gl_t a, gl_t b)
 
 GL_HD gl_t gl_neg(gl_t a) { return gl_sub(0, a); }
 
+// ---- add / subtract with the SECOND wrap left out and its occurrence counted ----
+// gl_add's second wrap needs both operands >= 2^64 - 2^32, gl_sub's needs b > 2^64 - 2^32 + a: 2^-64 per operation on
+// operands spread over the field, impossible between canonical operands -- but results in [p, 2^64) are legal here, so
+// crafted inputs can reach it.  These forms only COUNT the event (three / two instructions fewer) and leave the value
+// wrong when it fires; whoever uses them must discard the results and redo the work with gl_add / gl_sub when
+// gl_defer_hit() (the optimistic NTT passes raise a flag that the host checks, capi.cu dev_extend_pol_checked).
+// Two counters because the add form can only count up and the subtract form only down: one shared counter could cancel.
+struct GlDefer { uint32_t up, dn; };
+GL_HD bool gl_defer_hit(const GlDefer &f) { return (f.up | f.dn) != 0; }
+GL_HD gl_t gl_add_defer(gl_t a, gl_t b, GlDefer &f)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,m;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "add.cc.u32 a0, a0, b0;\n\t"
+        "addc.cc.u32 a1, a1, b1;\n\t"
+        "addc.u32 m, 0, 0;\n\t"
+        "sub.u32 m, 0, m;\n\t"                        // + EPS on carry
+        "add.cc.u32 a0, a0, m;\n\t"
+        "addc.cc.u32 a1, a1, 0;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"                     // up += second carry
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(r), "+r"(f.up) : "l"(a), "l"(b));
+    return r;
+#else
+    gl_t r = a + b;
+    if (r < a) { const gl_t r2 = r + GL_EPS; if (r2 < r) f.up++; r = r2; }
+    return r;
+#endif
+}
+GL_HD gl_t gl_sub_defer(gl_t a, gl_t b, GlDefer &f)
+{
+#if GL_DEVICE_PTX
+    gl_t r;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,m;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "sub.cc.u32 a0, a0, b0;\n\t"
+        "subc.cc.u32 a1, a1, b1;\n\t"
+        "subc.u32 m, 0, 0;\n\t"                       // 0xffffffff on borrow
+        "sub.cc.u32 a0, a0, m;\n\t"                   // - EPS on borrow
+        "subc.cc.u32 a1, a1, 0;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"                     // dn -= second borrow
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(r), "+r"(f.dn) : "l"(a), "l"(b));
+    return r;
+#else
+    gl_t r = a - b;
+    if (a < b) { const gl_t r2 = r - GL_EPS; if (r2 > r) f.dn--; r = r2; }
+    return r;
+#endif
+}
+template <bool DEFER> GL_HD gl_t gl_add_x(gl_t a, gl_t b, GlDefer &f) { return DEFER ? gl_add_defer(a, b, f) : gl_add(a, b); }
+template <bool DEFER> GL_HD gl_t gl_sub_x(gl_t a, gl_t b, GlDefer &f) { return DEFER ? gl_sub_defer(a, b, f) : gl_sub(a, b); }
+
 // fold a 128-bit value hi:lo to 64 bits (mod p); EPSALU picks the pipe of the p2*EPS term (see above)
 template <bool EPSALU>
 GL_HD gl_t gl_reduce128_t(gl_t lo, gl_t hi)

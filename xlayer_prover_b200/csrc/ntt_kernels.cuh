@@ -74,6 +74,7 @@ struct NttPass {
     uint32_t nparts, log_part_rows;
     uint64_t part_pitch, part_col0;
     uint32_t log_cw;                 // NARROW kernels: lanes per tile = 2^log_cw >= ncols (32 >> log_cw tiles share a warp)
+    uint32_t *defer_flag;            // OPTIMISTIC kernels: set to 1 when a deferred wrap fired (the results are then invalid)
 };
 
 static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
@@ -87,8 +88,10 @@ static constexpr __host__ __device__ int ntt_cbitrev(int x, int bits)
 // ---- in-register 2^LOG-point DIF transform, twiddles are powers of two ----
 // v[bitrev(u)] <- sum_m v[m] * w^(m u),  w = W[LOG] = 2^(192 / 2^LOG)   (W[4]=2^12, W[3]=2^24, W[2]=2^48, W[1]=2^96=-1)
 // LSH: inputs with index >= (2^LOG >> LSH) are zero (not even initialised); butterflies on them are pruned.
-template <int LOG, int LSH>
-static __device__ __forceinline__ void ntt_dft_regs(gl_t *v)
+// OPT (optimistic): butterflies on gl_add_defer / gl_sub_defer (13 instead of 18 instructions); the count of wraps that
+// were left out accumulates in f and the caller raises NttPass::defer_flag when it is non-zero.
+template <int LOG, int LSH, bool OPT>
+static __device__ __forceinline__ void ntt_dft_regs(gl_t *v, GlDefer &f)
 {
     constexpr int Q = 1 << LOG;
     constexpr int LIVE = Q >> LSH;
@@ -110,8 +113,8 @@ static __device__ __forceinline__ void ntt_dft_regs(gl_t *v)
                     }
                 } else {
                     const gl_t a = v[g + j], b = v[g + j + h];
-                    v[g + j] = gl_add(a, b);
-                    const gl_t d = gl_sub(a, b);
+                    v[g + j] = gl_add_x<OPT>(a, b, f);
+                    const gl_t d = gl_sub_x<OPT>(a, b, f);
                     v[g + j + h] = (j == 0) ? d : gl_mul_pow2(d, (unsigned)(tshift * j));
                 }
             }
@@ -202,7 +205,7 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
 // row, becomes a per-lane quantity instead of a warp-uniform one.  Everything else is the same code.
 // The body works on the tile(s) of virtual block index vbx with `nwarps` warps (k_ntt_pass: vbx = blockIdx.x, 16 warps;
 // k_ntt_pass_co: a small resident grid walks the block indices, see below).
-template <int A, int B, bool INV, int LSH, bool NARROW>
+template <int A, int B, bool INV, int LSH, bool NARROW, bool OPT = false>
 static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *tile, const uint32_t vbx, const uint32_t nwarps)
 {
     constexpr int QA = 1 << A, QB = 1 << B, LOGQ = A + B;
@@ -274,7 +277,9 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
                 v[m] = gl_mul_fma(v[m], f);
             }
         }
-        ntt_dft_regs<A, LSH>(v);
+        GlDefer f = {0, 0};
+        ntt_dft_regs<A, LSH, OPT>(v, f);
+        if (OPT && gl_defer_hit(f)) *a.defer_flag = 1u;
         if (B == 0) {
             ntt_store_outputs<A, INV>(a, sl, v, 0, 1, p, omul, fptr, fsh, fkind, fbase, fbsh, rbase, rsh, col, colok);
         } else {
@@ -299,7 +304,9 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
         const gl_t *trow = tile + (size_t)u * QB * NTT_LANES + lane;
 #pragma unroll
         for (int b = 0; b < QB; b++) v[b] = trow[(size_t)b * NTT_LANES];
-        ntt_dft_regs<B, 0>(v);
+        GlDefer f = {0, 0};
+        ntt_dft_regs<B, 0, OPT>(v, f);
+        if (OPT && gl_defer_hit(f)) *a.defer_flag = 1u;
         ntt_store_outputs<B, INV>(a, sl, v, u, QA, p, omul, fptr, fsh, fkind, fbase, fbsh, rbase, rsh, col, colok);
     }
 }
@@ -310,6 +317,19 @@ k_ntt_pass(NttPass a)
 {
     GLP_DYN_SMEM(gl_t, tile);                                    // [Q][32] when B > 0
     ntt_pass_block<A, B, INV, LSH, NARROW>(a, tile, blockIdx.x, NTT_WARPS);
+}
+// The optimistic flavour of the wide two-step passes: same tile pass on the deferred add / subtract.  Its results are
+// valid only if a.defer_flag is still zero when the whole transform has finished; dev_extend_pol_checked (capi.cu) reads
+// the flag and runs the transform again with k_ntt_pass when it is not.  Recovery lives on the host because any recovery
+// code inside these 3000-instruction straight-line kernels costs what the shorter butterflies gain
+// (profiles/r01_ntt_experiments.txt).
+template <int A, int B, bool INV, int LSH>
+__global__ void __launch_bounds__(NTT_THREADS, NTT_MINBLOCKS)
+k_ntt_pass_opt(NttPass a)
+{
+    static_assert(B > 0, "optimistic passes are two-step tiles");
+    GLP_DYN_SMEM(gl_t, tile);
+    ntt_pass_block<A, B, INV, LSH, false, true>(a, tile, blockIdx.x, NTT_WARPS);
 }
 
 // Co-resident flavour (two-step tiles only): a grid of a few CTAs per SM, each of blockDim.x/32 <= 16 warps, walks
