@@ -165,16 +165,24 @@ def check_commit(ctx, oracle, a, n_ext, **kw):
     check_equal(root, want_tree[-4:], "commit root")
 
 
+NTT_MASK = 0x9E3779B97F4A7C15                      # xlayer_prover_b200/csrc/ntt_kernels.cuh
+
+
 def wrap_twice_matrix(rng, n, ncols):
     """Inputs that make the butterflies of the INTT's first two stages wrap TWICE: with rows r, r + n/4, r + n/2, r + 3n/4
     of a column set to (p-1, p-1, 2^32-1, 2^32-1) stage 1 leaves 2^64-1 in two registers (no carry, legal but >= p) and
     stage 2 adds them (second carry); with (0, p-1, 0, 2^32-1) stage 2 subtracts 2^64-1 from 0 (second borrow).  The
-    optimistic NTT passes (k_ntt_pass_opt) leave those wraps out, flag them, and the LDE is repeated exactly."""
+    optimistic NTT passes (k_ntt_pass_opt) leave those wraps out, flag them, and the LDE is repeated exactly.  (The values
+    are what the butterflies see; the matrix holds them divided by the input mask.)"""
     a = rng.integers(0, P, size=(n, ncols), dtype=np.uint64)
     q = n // 4
-    a[1, 0], a[1 + q, 0], a[1 + 2 * q, 0], a[1 + 3 * q, 0] = P - 1, P - 1, 2 ** 32 - 1, 2 ** 32 - 1
+    inv = pow(NTT_MASK, P - 2, P)                   # the optimistic LDE multiplies its inputs by NTT_MASK first
+
+    def pre(v):
+        return (v * inv) % P
+    a[1, 0], a[1 + q, 0], a[1 + 2 * q, 0], a[1 + 3 * q, 0] = pre(P - 1), pre(P - 1), pre(2 ** 32 - 1), pre(2 ** 32 - 1)
     c = ncols - 1
-    a[q - 1, c], a[2 * q - 1, c], a[3 * q - 1, c], a[4 * q - 1, c] = 0, P - 1, 0, 2 ** 32 - 1
+    a[q - 1, c], a[2 * q - 1, c], a[3 * q - 1, c], a[4 * q - 1, c] = 0, pre(P - 1), 0, pre(2 ** 32 - 1)
     return a
 
 
@@ -190,6 +198,11 @@ def check_optimistic_lde(make_ctx, oracle, rng, n=256, ncols=20):
         r0 = ctx.ntt_retry_count()
         check_equal(run_extend(ctx, honest, n_ext, device=True), oracle.extend_pol(honest, n_ext), "optimistic LDE, honest data")
         assert ctx.ntt_retry_count() == r0, "honest data must not need the exact passes"
+        small = rng.integers(0, 7, size=(n, ncols), dtype=np.uint64)             # a trace: 0, 1, small values and -1, -2
+        small[rng.random((n, ncols)) < 0.1] = P - 1
+        small[rng.random((n, ncols)) < 0.05] = P - 2
+        check_equal(run_extend(ctx, small, n_ext, device=True), oracle.extend_pol(small, n_ext), "optimistic LDE, trace-like data")
+        assert ctx.ntt_retry_count() == r0, "trace-like data must not need the exact passes (input mask)"
         check_equal(run_extend(ctx, crafted, n_ext, device=True), oracle.extend_pol(crafted, n_ext), "optimistic LDE, crafted data")
         assert ctx.ntt_retry_count() == r0 + 1, "crafted data must have been repeated with the exact passes"
         check_commit(ctx, oracle, crafted, n_ext, device=True)

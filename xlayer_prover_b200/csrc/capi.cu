@@ -416,18 +416,19 @@ static bool plan_passes(const glp_ctx *ctx, uint32_t logN, NttPlanLogs *pl)
     return true;
 }
 // shift^j/N in the storage order the DIF plan `pl` leaves coefficient j in
-static int get_scale_table(glp_ctx *ctx, uint32_t logN, const NttPlanLogs &pl, const gl_t **out)
+static int get_scale_table(glp_ctx *ctx, uint32_t logN, const NttPlanLogs &pl, const gl_t **out, bool masked = false)
 {
     *out = nullptr;
     if (logN > NTT_PASS_TABLE_MAX_LOGL || ctx->no_pass_tables) return GLP_OK;
-    uint64_t key = logN;
+    uint64_t key = logN | (masked ? 0x80u : 0u);                  // masked: shift^j / (N * NTT_MASK), for the optimistic LDE
     for (uint32_t i = 0; i < NTT_MAX_PASSES; i++) key = (key << 8) | (i < pl.npass ? pl.lg[i] : 0);
     auto it = ctx->scale_tabs.find(key);
     if (it == ctx->scale_tabs.end()) {
         gl_t *t = nullptr;
         const uint64_t n = 1ull << logN;
         GLP(table_alloc(ctx, n, &t));
-        LAUNCH_FLAT(ctx, k_ntt_scale_table, (unsigned)((n + 255) / 256), 256, t, host_ninv(logN), (gl_t)GL_SHIFT, pl, n);
+        const gl_t c = masked ? gl_canon(gl_mul(host_ninv(logN), gl_inv((gl_t)NTT_MASK))) : host_ninv(logN);
+        LAUNCH_FLAT(ctx, k_ntt_scale_table, (unsigned)((n + 255) / 256), 256, t, c, (gl_t)GL_SHIFT, pl, n);
         CU(cudaGetLastError());
         it = ctx->scale_tabs.emplace(key, t).first;
     }
@@ -483,7 +484,7 @@ static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t 
     do {                                                                             \
         if (narrow) NTT_GO2(INV, LSH, true);                                         \
         else if (B > 0 && A + B >= 7 && ctx->co_active) NTT_GO_CO(INV, LSH);         \
-        else if (B > 0 && A + B >= 6 && ctx->opt_active) NTT_GO_OPT(INV, LSH);       \
+        else if (B > 0 && A + B >= 6 && a.opt) NTT_GO_OPT(INV, LSH);       \
         else NTT_GO2(INV, LSH, false);                                               \
     } while (0)
     if (inv) NTT_GO(true, 0);
@@ -609,12 +610,17 @@ static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint
     r = q;
     r.lg[r.npass - 1] -= e;
     if (r.lg[r.npass - 1] == 0) r.npass--;
+    bool opt = false;
     // ---- INTT, DIF, in place in S ----
     {
         ProfScope ps(ctx, 0);
         if (r.npass == 0) GLP(copy_canon(ctx, S, wb, in, in_pitch, 1, wb));
         const gl_t *sct = nullptr;
         if (r.npass) GLP(get_scale_table(ctx, logN, r, &sct));
+        if (ctx->opt_active && sct) {                            // optimistic: masked inputs, mask undone by the scale table
+            GLP(get_scale_table(ctx, logN, r, &sct, true));
+            opt = true;
+        }
         uint32_t logL = logN;
         for (uint32_t i = 0; i < r.npass; i++) {
             const bool first = i == 0, last = i + 1 == r.npass;
@@ -633,6 +639,8 @@ static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint
             a.nprev = i;
             for (uint32_t k = 0; k < i; k++) a.prev_log[k] = r.lg[k];
             a.canon_in = first;
+            a.opt = opt;
+            if (first && opt) a.mask = (gl_t)NTT_MASK;
             if (last) {
                 if (sct) { a.scale_mode = NTT_SC_TABLE; a.sc = sct; }
                 else {
@@ -668,6 +676,7 @@ static int run_lde(glp_ctx *ctx, uint32_t logN, uint32_t e, const gl_t *in, uint
             a.tw_mode = first ? NTT_TW_NONE : NTT_TW_PRE;
             a.tw = tab;
             a.canon_out = last;
+            a.opt = opt;
             if (last && sc) {                                     // the exchange rides on the last pass's stores
                 a.parts = sc->parts;
                 a.nparts = sc->nparts;

@@ -75,6 +75,8 @@ struct NttPass {
     uint64_t part_pitch, part_col0;
     uint32_t log_cw;                 // NARROW kernels: lanes per tile = 2^log_cw >= ncols (32 >> log_cw tiles share a warp)
     uint32_t *defer_flag;            // OPTIMISTIC kernels: set to 1 when a deferred wrap fired (the results are then invalid)
+    uint32_t opt;                    // launch the optimistic flavour of this pass (set by run_lde for a masked transform)
+    gl_t mask;                       // first pass of an optimistic LDE (any kernel flavour): inputs times this constant instead of canonicalised
 };
 
 static __device__ __forceinline__ uint32_t ntt_bitrev(uint32_t x, uint32_t bits) { return bits ? (__brev(x) >> (32 - bits)) : 0; }
@@ -88,6 +90,15 @@ static constexpr __host__ __device__ int ntt_cbitrev(int x, int bits)
 // ---- in-register 2^LOG-point DIF transform, twiddles are powers of two ----
 // v[bitrev(u)] <- sum_m v[m] * w^(m u),  w = W[LOG] = 2^(192 / 2^LOG)   (W[4]=2^12, W[3]=2^24, W[2]=2^48, W[1]=2^96=-1)
 // LSH: inputs with index >= (2^LOG >> LSH) are zero (not even initialised); butterflies on them are pruned.
+// The optimistic passes are data-independent only on data that is spread over the field.  Real traces are not: they are
+// full of 0, 1 and small values, -1 + 5 is the legal non-canonical word p + 4, and 0 - (p + 4) wraps twice -- on such data
+// some lane always flags and the whole transform is repeated.  So an optimistic LDE multiplies every input by the fixed
+// constant R = NTT_MASK in its first pass (instead of canonicalising it: x*R folds any 64-bit x) and the INTT's last pass
+// multiplies by shift^j/(N*R) instead of shift^j/N (one scale table more): the transform is linear, the result is the
+// same, and what flows through the butterflies is s*R mod p, spread over the field for the small s of a trace
+// (profiles/r01_sweep_data_independence.jsonl).  Crafted data can still fire the flag; that only costs the repeat.
+#define NTT_MASK 0x9E3779B97F4A7C15ULL
+
 // OPT (optimistic): butterflies on gl_add_defer / gl_sub_defer (13 instead of 18 instructions); the count of wraps that
 // were left out accumulates in f and the caller raises NttPass::defer_flag when it is non-zero.
 template <int LOG, int LSH, bool OPT>
@@ -265,7 +276,10 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
             for (int m = 0; m < (QA >> LSH); m++)
                 v[m] = (colok && r0 + (uint64_t)m * rstep < a.live) ? in[(uint64_t)m * in_step] : 0;   // plain load: middle passes run in place
         }
-        if (a.canon_in) {
+        if (a.mask) {                                            // see NTT_MASK: x -> x*R, undone by the INTT's scale table
+#pragma unroll
+            for (int m = 0; m < (QA >> LSH); m++) v[m] = gl_mul_fma(v[m], a.mask);
+        } else if (a.canon_in) {
 #pragma unroll
             for (int m = 0; m < (QA >> LSH); m++) v[m] = gl_canon(v[m]);
         }
