@@ -7,4 +7,4 @@ timeout 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; ech
 tail -c 400 gpurun_out/bench.err
 cut -c1-700 gpurun_out/bench.json
 timeout 600 python tools/sweep.py dist > gpurun_out/sweep_dist.jsonl 2> gpurun_out/sweep_dist.err; echo "sweep rc=$?"; cat gpurun_out/sweep_dist.jsonl
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_opt.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_bench.log 2>&1; echo "ncu rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_final2.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_bench.log 2>&1; echo "ncu rc=$?"
