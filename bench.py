@@ -44,8 +44,9 @@ SEED = 0x9E3779B97F4A7C15 + 2          # seed = golden ratio + config
 POS_PIPE_CYCLES = {"fmaheavy": 25426, "fp64": 4368, "alu": 21712, "issue": 21905}
 POS_BOUND_CYCLES = POS_PIPE_CYCLES["fmaheavy"] + POS_PIPE_CYCLES["fp64"]
 # dram__bytes_read.sum + dram__bytes_write.sum of k_linear_hash_rows from the ncu --set full capture at 2^19 rows x 660
-# columns (profiles/r01_ncu_full_summary_call7.txt: 2.827875 GB + 21.34 MB), per row; a launch's traffic scales with its rows
-LEAF_DRAM_BYTES_PER_ROW_660 = (2.827875e9 + 21.341952e6) / (1 << 19)
+# columns (profiles/r01_ncu_full_summary_final2.txt, final binary of round 1: 2.834834 GB + 33.56 MB), per row; a launch's
+# traffic scales with its rows
+LEAF_DRAM_BYTES_PER_ROW_660 = (2.834834e9 + 33.558016e6) / (1 << 19)
 
 
 def parse_args():
@@ -403,7 +404,7 @@ def main_ours(args):
             "roofline": {"kernel": "k_linear_hash_rows", "bound": "hbm", "achieved": leaf_gbs, "peak": hbm_peak, "unit": "GB/s",
                          "frac": (leaf_gbs / hbm_peak) if leaf_gbs else None,
                          "traffic": LEAF_DRAM_BYTES_PER_ROW_660 * R if C == 660 else None,
-                         "traffic_note": "ncu dram bytes per launch, scaled from the 2^19-row capture by rows (2.3 % over the algorithmic bytes)" if C == 660 else None,
+                         "traffic_note": "ncu dram bytes per launch, scaled from the 2^19-row capture by rows (3.0 % over the algorithmic bytes)" if C == 660 else None,
                          "peak_source": peak_src,
                          "launch_ms": leaf_ms, "algorithmic_bytes_per_launch": leaf_bytes,
                          "note": "dominant kernel by time; it is integer-issue bound, not HBM bound -- see roofline_int"},
