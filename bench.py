@@ -41,7 +41,8 @@ SEED = 0x9E3779B97F4A7C15 + 2          # seed = golden ratio + config
 # trip counts 8/7/12/22) and the pipe costs measured on this GPU (profiles/r01_int_pipes.txt: IMAD.WIDE and IMAD.HI 4 cycles
 # per warp instruction per SM sub-partition, other IMAD, DFMA/DADD and every ALU op 2, one issue per cycle).  DFMA shares its
 # dispatch with IMAD.WIDE (DFMA+IMAD.WIDE pairs take 5.5 cycles, 6 if serial), so the multiplier bound counts both.
-POS_PIPE_CYCLES = {"fmaheavy": 25426, "fp64": 4368, "alu": 21712, "issue": 21905}
+# (alu / issue: the SASS count of the exact kernel minus the two ALU instructions the deferred wrap removes from each of the 748 folds)
+POS_PIPE_CYCLES = {"fmaheavy": 25426, "fp64": 4368, "alu": 21712 - 2 * 2 * 748, "issue": 21905 - 2 * 748}
 POS_BOUND_CYCLES = POS_PIPE_CYCLES["fmaheavy"] + POS_PIPE_CYCLES["fp64"]
 # dram__bytes_read.sum + dram__bytes_write.sum of k_linear_hash_rows from the ncu --set full capture at 2^19 rows x 660
 # columns (profiles/r01_ncu_full_summary_final2.txt, final binary of round 1: 2.834834 GB + 33.56 MB), per row; a launch's
