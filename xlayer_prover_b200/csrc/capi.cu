@@ -1499,9 +1499,33 @@ extern "C" int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint6
         GLP(commit_overlapped(ctx, dext, dtree, (const gl_t *)in, n, n_ext, ncols));
         if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     } else {
-        GLP(dev_extend_pol_checked(ctx, dext, ncols, (const gl_t *)in, ncols, n_ext, n, ncols));
-        if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
-        if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+        // Optimistic LDE (with_optimistic_ntt), but with the flag read at the END of the commit, behind the one synchronise
+        // the call makes anyway: the hash of an extension that turns out to be flagged is wasted, which never happens on
+        // honest data, and the common path has no host round trip between the LDE and the hash.
+        const gl_t *din = (const gl_t *)in, *in_end = din + (n - 1) * ncols + ncols, *ext_end = dext + ext_words;
+        bool opt = ctx->opt_enabled && !ctx->no_fused_lde && (in_end <= dext || ext_end <= din);
+        for (;;) {
+            if (opt) {
+                if (!ctx->opt_flag_dev) {
+                    CU(cudaMalloc((void **)&ctx->opt_flag_dev, sizeof(uint32_t)));
+                    CU(cudaHostAlloc((void **)&ctx->opt_flag_host, sizeof(uint32_t), cudaHostAllocDefault));
+                }
+                CU(cudaMemsetAsync(ctx->opt_flag_dev, 0, sizeof(uint32_t), ctx->stream));
+            }
+            ctx->opt_active = opt;
+            const int rc = dev_extend_pol(ctx, dext, ncols, din, ncols, n_ext, n, ncols);
+            ctx->opt_active = false;
+            if (rc != GLP_OK) return rc;
+            if (opt) CU(cudaMemcpyAsync(ctx->opt_flag_host, ctx->opt_flag_dev, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            if (out_ext && !ext_dev) CU(cudaMemcpyAsync(out_ext, dext, ext_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+            if (want_tree) GLP(dev_merkletree(ctx, dtree, dext, ncols, ncols, n_ext));
+            if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+            if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            if (!opt || !(*ctx->opt_flag_host || ctx->opt_force_retry)) return GLP_OK;
+            ctx->opt_retries++;                                  // flagged: everything again with the exact passes
+            opt = false;
+        }
     }
     if (tree && !tree_dev) CU(cudaMemcpyAsync(tree, dtree, tree_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     if (root) CU(cudaMemcpyAsync(root, dtree + tree_words - 4, 4 * sizeof(gl_t), cudaMemcpyDefault, ctx->stream));

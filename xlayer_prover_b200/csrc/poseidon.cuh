@@ -122,6 +122,32 @@ GL_HD gl_t pos_fold128(gl_t lo, gl_t hi, uint32_t &bf)
 #endif
 // value = Z + X*2^32 + Y*2^64  ->  limbs l0..l4 (weights 2^0..2^128), then
 //   (l1:l0) + l2*EPS - l3 - l4*2^32   (2^64 = EPS, 2^96 = -1, 2^128 = -2^32)
+#ifndef POS_DEFER_DOTSUB
+#define POS_DEFER_DOTSUB 1        // deferred rows: the dot-product folds' last subtraction leaves its (2^-28) wrap to the redo as well
+#endif
+#ifndef POS_MDS_FOLD_FMA
+#define POS_MDS_FOLD_FMA 1        // top*EPS of the MDS fold as IMAD + IMAD.HI (6 pipe cycles) instead of four ALU instructions (8)
+#endif                            // (each +0.5 % on the leaf hash, profiles/r01_poseidon_defer.txt)
+// r - b for b < 2^40 with the (rare: r < b) wrap left out and counted in bf, like gl_reduce128_defer
+GL_HD gl_t gl_sub_small_defer(gl_t r, gl_t b, uint32_t &bf)
+{
+#if GL_DEVICE_PTX
+    gl_t o;
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "sub.cc.u32 a0, a0, b0;\n\t"
+        "subc.cc.u32 a1, a1, b1;\n\t"
+        "subc.u32 %1, %1, 0;\n\t"
+        "mov.b64 %0, {a0,a1};\n\t"
+        "}" : "=l"(o), "+r"(bf) : "l"(r), "l"(b));
+    return o;
+#else
+    (void)bf;
+    return gl_sub(r, b);
+#endif
+}
 template <bool DEFER>
 GL_HD gl_t gl_dot_fold(const GlDotAcc &s, uint32_t &bf)
 {
@@ -132,6 +158,9 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s, uint32_t &bf)
     gl_t lo = ((t1 & 0xFFFFFFFFULL) << 32) | s.z0;
     gl_t hi = ((t3 & 0xFFFFFFFFULL) << 32) | (t2 & 0xFFFFFFFFULL);
     gl_t r = pos_fold128<DEFER, POS_FOLD_MODE>(lo, hi, bf);
+#if POS_DEFER_DOTSUB
+    if (DEFER) return gl_sub_small_defer(r, l4 << 32, bf);      // l4 < 2^8: borrows with probability < 2^-24, never twice
+#endif
     return gl_sub(r, l4 << 32);
 }
 
@@ -165,7 +194,11 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
         "mov.b64 {h0,h1}, %2;\n\t"
         "add.cc.u32 l1, l1, h0;\n\t"
         "addc.u32 h1, h1, 0;\n\t"
+#if POS_MDS_FOLD_FMA
+        GL_PTX_ADD_EPS_MUL_FMA("l0", "l1", "h1")
+#else
         GL_PTX_ADD_EPS_MUL_ALU("l0", "l1", "h1")
+#endif
         "addc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 l0, l0, m;\n\t"
         "subc.u32 l1, l1, 0;\n\t"
