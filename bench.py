@@ -89,6 +89,8 @@ class ClockSampler:
         self.index, self.proc, self.lines = index, None, []
 
     def start(self):
+        if os.environ.get("BENCH_NO_CLOCK_SAMPLER"):       # diagnostics only (tools/gap_probe.sh): is the sampler itself visible in the timing?
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "200"],
