@@ -113,6 +113,16 @@ def test_linear_hash_deferred_wrap_rows_are_redone(ctx, oracle, rng):
     ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, 48:]), ncols - 48, ncols - 48, nrows, first=False)
     check_equal(cap, want, "absorb in two blocks with rows that take the exact path")
     assert ctx.leaf_redo_rows() - before >= 3 * len(crafted)
+    # tree nodes: rows of <= 4 columns are copied into the leaves unhashed, so crafted words reach the level-0 pair hashes
+    b = edge_matrix(rng, 1 << 10, 4)
+    made = 0
+    for k, row in enumerate(range(3, 1 << 10, 41)):
+        pos = (k % 4) + 4 * (row & 1)                      # word of the 8-word pair this row's column k % 4 becomes
+        b[row, k % 4] = ((0xFFFFFFFE - k) << 32) - rc[pos]
+        made += 1
+    before = ctx.leaf_redo_rows()
+    check_equal(run_merkletree(ctx, b, device=True), oracle.merkletree(b), "merkletree whose level-0 nodes take the exact path")
+    assert ctx.leaf_redo_rows() - before >= made
 
 
 def test_optimistic_lde_is_repeated_exactly_when_flagged(oracle, rng):

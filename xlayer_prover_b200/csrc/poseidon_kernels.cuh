@@ -133,8 +133,8 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     }
 }
 
-// parents[i] = H(children[2i] || children[2i+1] || 0000)[0:4]
-static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src)
+// parents[i] = H(children[2i] || children[2i+1] || 0000)[0:4]; the same deferred wrap and exact redo as the leaf rows
+static __device__ GLP_NOINLINE void pos_hash_pair_exact(gl_t *dst, const gl_t *src)
 {
     gl_t x[12];
 #pragma unroll
@@ -142,6 +142,25 @@ static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, con
 #pragma unroll
     for (int i = 8; i < 12; i++) x[i] = 0;
     pos_permute(x);
+#pragma unroll
+    for (int i = 0; i < 4; i++) dst[i] = gl_canon(x[i]);
+#if !defined(GLP_EMU)
+    atomicAdd(&g_pos_redo_rows, 1ull);
+#endif
+}
+static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src)
+{
+    gl_t x[12];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = src[i];
+#pragma unroll
+    for (int i = 8; i < 12; i++) x[i] = 0;
+    uint32_t bf = 0;
+    pos_permute_t<false, POS_DEFER_BORROW != 0>(x, bf);
+    if (POS_DEFER_BORROW && bf) {
+        pos_hash_pair_exact(dst, src);
+        return;
+    }
 #pragma unroll
     for (int i = 0; i < 4; i++) dst[i] = gl_canon(x[i]);
 }
