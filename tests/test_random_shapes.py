@@ -51,7 +51,7 @@ def test_random_shapes_emulator(ectx, oracle, s):
 
 
 @pytest.mark.gpu
-@settings(max_examples=60, **COMMON)
+@settings(max_examples=int(os.environ.get("GLP_FUZZ_EXAMPLES", "60")), **COMMON)      # GLP_FUZZ_EXAMPLES=1000 for a long run
 @given(st.tuples(st.integers(0, 15), st.integers(1, 130), st.integers(0, 4), st.integers(0, 2 ** 32 - 1), st.booleans()))
 def test_random_shapes_gpu(ctx, oracle, s):
     logn, ncols, logb, seed, device = s
