@@ -186,6 +186,10 @@ int glp_get_profile(glp_ctx *ctx, float ms[4], uint32_t count[4]);
 /* Dependent-free integer micro-benchmarks on this device: ops_per_s[0] = IMAD (32-bit multiply-add, the IMAD.WIDE pipe) lane-ops/s,
  * [1] = 32-bit add lane-ops/s (two adds fused as IADD3 count as one), [2] = both interleaved (sum of lane-ops/s). */
 int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3]);
+/* The same three plus [3] = IMAD.WIDE (32x32 -> 64 with a 64-bit accumulate) and [4] = DFMA lane-ops/s: the two instruction
+ * classes the algorithmic floor of one Poseidon permutation is counted in (1122 field multiplies x 4 IMAD.WIDE + 7 MDS layers
+ * x 288 DFMA; bench.py `roofline`). */
+int glp_measure_pipe_peaks(glp_ctx *ctx, double ops_per_s[5]);
 
 #ifdef __cplusplus
 }

@@ -301,3 +301,52 @@ def check_fri_layers(ctx, reference, rng, pol_bits=10, steps=(7, 4, 2)):
         for _ in range(bits - nb):
             shift_inv = shift_inv * shift_inv % P
         pol, bits = want, nb
+
+
+def check_deferred_rows(ctx, oracle, rng, nrows=4096, device=False):
+    """Rows that make a deferred fold of the leaf hash go wrong, so that the exact redo must run (gl_fold_defer_raw).
+    On random data that is one row in 10^5, so drive it.  Form 2 of the fold (the S-boxes) computes t = lo64 + p2*EPS and
+    then t - p3 with the borrow left out: a state word y = c * 2^48 (c < 2^16) squares to c^2 * 2^96, i.e. lo64 = 0,
+    p2 = 0, p3 = c^2 > t = 0.  Form 1 (rank-1 updates, dot products) leaves out the borrow of lo64 - p3; its flag word is
+    the high word of lo64, which the same rows drive to zero in the first S-box layer.  Rows carry such a word at every
+    rate position and in several sponge blocks; the results must equal the oracle and every crafted row must be redone."""
+    import pathlib
+    import re
+    src = (pathlib.Path(__file__).resolve().parents[1] / "xlayer_prover_b200" / "csrc" / "poseidon_tables.cuh").read_text()
+    rc = [int(v, 16) for v in re.findall(r"0x[0-9a-fA-F]{16}", src.split("GLP_POSEIDON_RC_INIT", 1)[1])[:8]]
+    P = 0xFFFFFFFF00000001
+    ncols = 100
+    a = edge_matrix(rng, nrows, ncols)
+    crafted = []
+    for k, row in enumerate(range(5, nrows, 97)):
+        pos, blk = k % 8, (k // 8) % 12
+        y = (0xFFFE - k) << 48                            # canonical, above every round constant, low 48 bits zero
+        assert rc[pos] <= y < P
+        a[row, 8 * blk + pos] = y - rc[pos]               # + RC[pos] = y exactly
+        crafted.append(row)
+    want = oracle.linear_hash_rows(a)
+    before = ctx.leaf_redo_rows()
+    got = np.zeros((nrows, 4), dtype=np.uint64)
+    ctx.linear_hash_rows(got, a, ncols, ncols, nrows)
+    check_equal(got, want, "linear_hash with rows that take the exact path")
+    redone = ctx.leaf_redo_rows() - before
+    assert redone >= len(crafted), (redone, len(crafted))
+    # the same rows as leaves of a tree and through the sponge continuation (cap_in aliases out)
+    tree = run_merkletree(ctx, a, device=device)
+    check_equal(tree, oracle.merkletree(a), "merkletree with rows that take the exact path")
+    cap = np.zeros((nrows, 4), dtype=np.uint64)
+    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, :48]), 48, 48, nrows, first=True)
+    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, 48:]), ncols - 48, ncols - 48, nrows, first=False)
+    check_equal(cap, want, "absorb in two blocks with rows that take the exact path")
+    assert ctx.leaf_redo_rows() - before >= 3 * len(crafted)
+    # tree nodes: rows of <= 4 columns are copied into the leaves unhashed, so crafted words reach the level-0 pair hashes
+    nb = min(nrows, 1 << 10)
+    b = edge_matrix(rng, nb, 4)
+    made = 0
+    for k, row in enumerate(range(3, nb, 41)):
+        pos = (k % 4) + 4 * (row & 1)                      # word of the 8-word pair this row's column k % 4 becomes
+        b[row, k % 4] = ((0xFFFE - k) << 48) - rc[pos]
+        made += 1
+    before = ctx.leaf_redo_rows()
+    check_equal(run_merkletree(ctx, b, device=device), oracle.merkletree(b), "merkletree whose level-0 nodes take the exact path")
+    assert ctx.leaf_redo_rows() - before >= made

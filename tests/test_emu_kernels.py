@@ -74,6 +74,12 @@ def test_linear_hash_and_tree(ectx, oracle, golden, fixtures, rng):
     check_equal(run_merkletree(ectx, a, dim=3), oracle.merkletree(a), "dim=3")
 
 
+def test_deferred_fold_rows_are_redone(ectx, oracle, rng):
+    """the emulator's portable folds model the deferral (value left wrong, event recorded), so the redo paths run here too"""
+    from cases import check_deferred_rows
+    check_deferred_rows(ectx, oracle, rng, nrows=512)
+
+
 def check_merkletree_batch(ctx, oracle, golden, rng):
     a = fib_matrix(64, 128)
     tree = np.zeros(tree_words(64), dtype=np.uint64)

@@ -81,48 +81,10 @@ def test_linear_hash_kat_and_sizes(ctx, oracle, golden, rng):
 
 
 def test_linear_hash_deferred_wrap_rows_are_redone(ctx, oracle, rng):
-    """The leaf kernel's fast path leaves the (lo64 of a product) < (its top word) wrap of a fold uncorrected and, when it
-    fires, hashes the row again with the exact fold (poseidon_kernels.cuh, POS_DEFER_BORROW).  On random data that is one
-    row in 10^5, so drive it: a state word y = a * 2^32 (a >= 2^16) squares to lo64 = 0, top word = a^2 >> 32 > 0 in the
-    first S-box layer.  Rows carry such a word at every rate position and in several sponge blocks."""
-    import re, pathlib
-    src = (pathlib.Path(__file__).resolve().parents[1] / "xlayer_prover_b200" / "csrc" / "poseidon_tables.cuh").read_text()
-    rc = [int(v, 16) for v in re.findall(r"0x[0-9a-fA-F]{16}", src.split("GLP_POSEIDON_RC_INIT", 1)[1])[:8]]
-    P = 0xFFFFFFFF00000001
-    ncols, nrows = 100, 4096
-    a = edge_matrix(rng, nrows, ncols)
-    crafted = []
-    for k, row in enumerate(range(5, nrows, 97)):
-        pos, blk = k % 8, (k // 8) % 12
-        y = (0xFFFFFFFE - k) << 32                        # canonical, above every round constant, low 32 bits zero
-        assert rc[pos] <= y < P
-        a[row, 8 * blk + pos] = y - rc[pos]               # + RC[pos] = y exactly
-        crafted.append(row)
-    want = oracle.linear_hash_rows(a)
-    before = ctx.leaf_redo_rows()
-    got = np.zeros((nrows, 4), dtype=np.uint64)
-    ctx.linear_hash_rows(got, a, ncols, ncols, nrows)
-    check_equal(got, want, "linear_hash with rows that take the exact path")
-    redone = ctx.leaf_redo_rows() - before
-    assert redone >= len(crafted), (redone, len(crafted))
-    # the same rows as leaves of a tree and through the sponge continuation (cap_in aliases out)
-    tree = run_merkletree(ctx, a, device=True)
-    check_equal(tree, oracle.merkletree(a), "merkletree with rows that take the exact path")
-    cap = np.zeros((nrows, 4), dtype=np.uint64)
-    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, :48]), 48, 48, nrows, first=True)
-    ctx.linear_hash_absorb(cap, np.ascontiguousarray(a[:, 48:]), ncols - 48, ncols - 48, nrows, first=False)
-    check_equal(cap, want, "absorb in two blocks with rows that take the exact path")
-    assert ctx.leaf_redo_rows() - before >= 3 * len(crafted)
-    # tree nodes: rows of <= 4 columns are copied into the leaves unhashed, so crafted words reach the level-0 pair hashes
-    b = edge_matrix(rng, 1 << 10, 4)
-    made = 0
-    for k, row in enumerate(range(3, 1 << 10, 41)):
-        pos = (k % 4) + 4 * (row & 1)                      # word of the 8-word pair this row's column k % 4 becomes
-        b[row, k % 4] = ((0xFFFFFFFE - k) << 32) - rc[pos]
-        made += 1
-    before = ctx.leaf_redo_rows()
-    check_equal(run_merkletree(ctx, b, device=True), oracle.merkletree(b), "merkletree whose level-0 nodes take the exact path")
-    assert ctx.leaf_redo_rows() - before >= made
+    """The leaf kernel's fast path leaves the rare wrap of every fold uncorrected and, when it may have fired, hashes the
+    row again with the exact fold (poseidon_kernels.cuh, POS_DEFER_BORROW): crafted rows, leaves and level-0 nodes."""
+    from cases import check_deferred_rows
+    check_deferred_rows(ctx, oracle, rng, device=True)
 
 
 def test_optimistic_lde_is_repeated_exactly_when_flagged(oracle, rng):

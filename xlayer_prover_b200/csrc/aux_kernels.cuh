@@ -125,6 +125,35 @@ __global__ void k_int_peak(uint64_t *sink, uint32_t iters, int mode)
 #define GLP_MADW(acc, y) acc = acc * (y) + a
 #define GLP_ADD3(acc, x, y) acc += (x) + (y)
 #endif
+    if (mode >= 3) {
+        // mode 3: 8 independent IMAD.WIDE chains (32x32 -> 64 with a 64-bit accumulate, written as the mad.lo.cc / madc.hi pair
+        // ptxas keeps as ONE instruction); mode 4: 8 independent DFMA chains.  The two instruction classes the algorithmic
+        // floor of the Poseidon permutation is made of (bench.py roofline).
+        double d0 = (double)a, d1 = (double)b, d2 = d0 + 1.0, d3 = d1 + 2.0, d4 = d0 + 3.0, d5 = d1 + 4.0, d6 = d0 + 5.0, d7 = d1 + 6.0;
+        const double dm = 1.0000000001, dc = 3.0;
+#if GL_DEVICE_PTX
+#define GLP_MADWIDE(lo, hi, y) asm volatile("{ mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.u32 %1, %2, %3, %1; }" : "+r"(lo), "+r"(hi) : "r"(y), "r"(a))
+#define GLP_DFMA(acc) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(acc) : "d"(dm), "d"(dc))
+#else
+#define GLP_MADWIDE(lo, hi, y) { uint64_t t_ = (((uint64_t)(hi) << 32) | (lo)) + (uint64_t)(y) * a; lo = (uint32_t)t_; hi = (uint32_t)(t_ >> 32); }
+#define GLP_DFMA(acc) acc = acc * dm + dc
+#endif
+        for (uint32_t i = 0; i < iters; i++) {
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                if (mode == 3) {
+                    GLP_MADWIDE(m0, s0, b); GLP_MADWIDE(m1, s1, b); GLP_MADWIDE(m2, s2, b); GLP_MADWIDE(m3, s3, b);
+                    GLP_MADWIDE(m4, s4, b); GLP_MADWIDE(m5, s5, b); GLP_MADWIDE(m6, s6, b); GLP_MADWIDE(m7, s7, b);
+                } else {
+                    GLP_DFMA(d0); GLP_DFMA(d1); GLP_DFMA(d2); GLP_DFMA(d3); GLP_DFMA(d4); GLP_DFMA(d5); GLP_DFMA(d6); GLP_DFMA(d7);
+                }
+            }
+        }
+        const double ds = d0 + d1 + d2 + d3 + d4 + d5 + d6 + d7;
+        const uint32_t rr = m0 ^ m1 ^ m2 ^ m3 ^ m4 ^ m5 ^ m6 ^ m7 ^ s0 ^ s1 ^ s2 ^ s3 ^ s4 ^ s5 ^ s6 ^ s7;
+        if (rr == iters * 0x9E3779B1u + 7u || ds == 0.125) sink[0] = rr;
+        return;
+    }
     for (uint32_t i = 0; i < iters; i++) {
 #pragma unroll
         for (int r = 0; r < 8; r++) {

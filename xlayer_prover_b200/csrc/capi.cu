@@ -239,6 +239,7 @@ extern "C" uint64_t glp_leaf_redo_rows(glp_ctx *ctx)
         cudaMemcpyFromSymbol(&n, g_pos_redo_rows, sizeof n) != cudaSuccess) { cudaGetLastError(); return 0; }
 #else
     (void)ctx;
+    n = __atomic_load_n(&g_pos_redo_rows, __ATOMIC_RELAXED);
 #endif
     return n;
 }
@@ -1757,9 +1758,8 @@ extern "C" int glp_get_profile(glp_ctx *ctx, float ms[4], uint32_t count[4])
     cudaGetLastError();
     return GLP_OK;
 }
-extern "C" int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3])
+static int measure_pipe_modes(glp_ctx *ctx, double *ops_per_s, int nmodes)
 {
-    if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_int_peak: NULL argument");
     CU(cudaSetDevice(ctx->device));
     GLP(ensure(ctx, ctx->partial, 2 * 148 * 8 * sizeof(gl_t)));
     cudaEvent_t a, b;
@@ -1767,7 +1767,7 @@ extern "C" int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3])
     CU(cudaEventCreate(&b));
     const unsigned grid = 148 * 8, block = 256;
     const uint32_t iters = 4096;
-    for (int mode = 0; mode < 3; mode++) {
+    for (int mode = 0; mode < nmodes; mode++) {
         LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, 64u, mode);      // warm-up
         CU(cudaEventRecord(a, ctx->stream));
         LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, iters, mode);
@@ -1781,4 +1781,14 @@ extern "C" int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3])
     cudaEventDestroy(a);
     cudaEventDestroy(b);
     return GLP_OK;
+}
+extern "C" int glp_measure_int_peak(glp_ctx *ctx, double ops_per_s[3])
+{
+    if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_int_peak: NULL argument");
+    return measure_pipe_modes(ctx, ops_per_s, 3);
+}
+extern "C" int glp_measure_pipe_peaks(glp_ctx *ctx, double ops_per_s[5])
+{
+    if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_pipe_peaks: NULL argument");
+    return measure_pipe_modes(ctx, ops_per_s, 5);
 }

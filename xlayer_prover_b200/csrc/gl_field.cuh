@@ -277,11 +277,111 @@ GL_HD gl_t gl_reduce128_wide(gl_t lo, gl_t hi)
 }
 // The fold with its RARE wrap deferred.  (p1:p0) - p3 borrows only when the low 64 bits of a product are below p3 < 2^32:
 // probability 2^-33 per fold on anything but crafted data, yet its fix-up (three instructions) runs every time.  Here the
-// borrow is only COUNTED into `bf` (bf -= borrow, one instruction) and the value is left wrong when it happens; the
-// caller must redo its whole computation with the exact fold whenever bf != 0 (k_linear_hash_rows redoes the row).
-// (Variants measured and dropped, profiles/r01_poseidon_defer.txt: the gl_reduce128_wide form with ITS 2^-32 borrow
-// deferred, all on the ALU pipe or with one IMAD.WIDE, and the carry fix-up moved to the multiplier pipe -- equal or slower.)
-GL_HD gl_t gl_reduce128_defer(gl_t lo, gl_t hi, uint32_t &bf)
+// event is only RECORDED in `bf` and the value is left wrong when it happens; the caller must redo its whole computation
+// with the exact fold whenever gl_borrow_hit(bf) (k_linear_hash_rows redoes the row).
+//
+// Recording (GL_BORROW_MIN 1): the fold hands back the 32-bit word `w` that must be ZERO for the event to be possible and
+// the caller keeps bf.zmin = min(bf.zmin, w); zmin == 0 at the end is the (conservative, 2^-32 per fold) sign.  Two folds
+// share one three-input VIMNMX3 (gl_borrow_note2): half an instruction per fold, and nothing hangs off the fold's carry
+// chain.  GL_BORROW_MIN 0 is round 1's form: bf.cnt -= borrow, one carry-chain instruction per fold.
+//
+// Forms of the fold itself (GL_FOLD_WIDE), SASS per fold next to the 4 IMAD.WIDE + 4 of the product (tools/sass_leaf.py):
+//   0 : t = (p1:p0) - p3; t += p2*EPS with the literal 0xffffffff, which ptxas turns into IMAD.HI + IMAD.IADD;
+//       + carry*EPS.                                                             2 multiplier-pipe + 5 other (round 1)
+//   1 : the same with EPS read from the constant bank: ptxas keeps ONE IMAD.WIDE with carry-out.   1 + 5
+//   2 : the multiply first, then both corrections in one subtraction:
+//           t = (p1:p0) + p2*EPS, carry m        (t <= 2^64 - 2^33 when m = 1)
+//           r = t - (p3 + m) + (m << 32)         (= t - p3 + m*EPS; 2^64 = EPS)                     1 + 4
+//       r < 0 needs m = 0 and t < p3, i.e. the high word of t zero: that word is `w`.  p3 + m must not overflow: for a
+//       product a*b, and for a*b + c with b < p (the Poseidon constants are canonical), p3 = 2^32 - 1 forces m = 0 (see
+//       DESIGN.md K6); a general 128-bit value (the dot-product accumulators) can have both, so PRODUCT = false takes form 1.
+// (Dropped in round 1, profiles/r01_poseidon_defer.txt: the gl_reduce128_wide form with ITS 2^-32 borrow deferred, all on
+// the ALU pipe, the carry fix-up on the multiplier pipe -- equal or slower.)
+#ifndef GL_BORROW_MIN
+#define GL_BORROW_MIN 1
+#endif
+#ifndef GL_FOLD_WIDE
+#define GL_FOLD_WIDE 2
+#endif
+struct GlBorrow { uint32_t cnt, zmin; };
+GL_HD GlBorrow gl_borrow_init() { GlBorrow b; b.cnt = 0; b.zmin = 0xffffffffu; return b; }
+GL_HD bool gl_borrow_hit(const GlBorrow &b) { return b.cnt != 0 || b.zmin == 0; }
+GL_HD uint32_t gl_min3(uint32_t a, uint32_t b, uint32_t c)
+{
+#if GL_DEVICE_PTX
+    return __vimin3_u32(a, b, c);                                 // VIMNMX3.U32
+#else
+    const uint32_t t = a < b ? a : b;
+    return t < c ? t : c;
+#endif
+}
+GL_HD void gl_borrow_note(GlBorrow &bf, uint32_t w) { bf.zmin = bf.zmin < w ? bf.zmin : w; }
+GL_HD void gl_borrow_note2(GlBorrow &bf, uint32_t wa, uint32_t wb) { bf.zmin = gl_min3(bf.zmin, wa, wb); }
+
+// hi:lo -> 64 bits, rare wrap left out; w = the word that is zero whenever the wrap was possible (GL_BORROW_MIN)
+template <bool PRODUCT>
+GL_HD gl_t gl_fold_defer_raw(gl_t lo, gl_t hi, uint32_t &w)
+{
+    constexpr bool V2 = PRODUCT && GL_FOLD_WIDE == 2;
+#if GL_DEVICE_PTX
+    gl_t r;
+    if (V2) {
+        asm("{\n\t"
+            ".reg .u32 p0,p1,p2,p3,m;\n\t"
+            "mov.b64 {p0,p1}, %2;\n\t"
+            "mov.b64 {p2,p3}, %3;\n\t"
+            "mad.lo.cc.u32 p0, p2, %4, p0;\n\t"
+            "madc.hi.cc.u32 p1, p2, %4, p1;\n\t"
+            "addc.u32 m, 0, 0;\n\t"
+            "mov.b32 %1, p1;\n\t"
+            "add.u32 p3, p3, m;\n\t"
+            "sub.cc.u32 p0, p0, p3;\n\t"
+            "subc.u32 p1, p1, 0;\n\t"
+            "add.u32 p1, p1, m;\n\t"
+            "mov.b64 %0, {p0,p1};\n\t"
+            "}" : "=l"(r), "=r"(w) : "l"(lo), "l"(hi), "r"(GL_EPS_OPAQUE));
+        return r;
+    }
+    w = (uint32_t)(lo >> 32);
+#if GL_FOLD_WIDE
+#define GL_DEFER_MUL "mad.lo.cc.u32 p0, p2, %3, p0;\n\t" "madc.hi.cc.u32 p1, p2, %3, p1;\n\t"
+#else
+#define GL_DEFER_MUL GL_PTX_ADD_EPS_MUL_FMA("p0", "p1", "p2")
+#endif
+    asm("{\n\t"
+        ".reg .u32 p0,p1,p2,p3,m;\n\t"
+        "mov.b64 {p0,p1}, %1;\n\t"
+        "mov.b64 {p2,p3}, %2;\n\t"
+        "sub.cc.u32 p0, p0, p3;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        GL_DEFER_MUL
+        "addc.u32 m, 0, 0;\n\t"
+        "sub.cc.u32 p0, p0, m;\n\t"
+        "subc.u32 p1, p1, 0;\n\t"
+        "add.u32 p1, p1, m;\n\t"
+        "mov.b64 %0, {p0,p1};\n\t"
+        "}" : "=l"(r) : "l"(lo), "l"(hi), "r"(GL_EPS_OPAQUE));
+#undef GL_DEFER_MUL
+    return r;
+#else
+    // the emulator models the deferral (value left unfixed, word handed back) so that the redo paths run on the CPU too
+    const uint32_t h0 = (uint32_t)hi, h1 = (uint32_t)(hi >> 32);
+    const gl_t u = ((gl_t)h0 << 32) - h0;
+    if (V2) {
+        const gl_t t = lo + u;
+        const uint32_t m = t < u;
+        w = (uint32_t)(t >> 32);
+        return t - (gl_t)(uint32_t)(h1 + m) + ((gl_t)m << 32);    // no fix-up when this goes below zero
+    }
+    w = (uint32_t)(lo >> 32);
+    const gl_t t = lo - h1;                                       // no -EPS fix-up when this borrows
+    gl_t r = t + u;
+    if (r < u) r += GL_EPS;
+    return r;
+#endif
+}
+// round 1's recording: the borrow is counted on the carry chain
+GL_HD gl_t gl_fold_defer_cnt(gl_t lo, gl_t hi, uint32_t &cnt)
 {
 #if GL_DEVICE_PTX
     gl_t r;
@@ -291,20 +391,37 @@ GL_HD gl_t gl_reduce128_defer(gl_t lo, gl_t hi, uint32_t &bf)
         "mov.b64 {p2,p3}, %3;\n\t"
         "sub.cc.u32 p0, p0, p3;\n\t"
         "subc.cc.u32 p1, p1, 0;\n\t"
-        "subc.u32 %1, %1, 0;\n\t"                     // bf -= borrow
+        "subc.u32 %1, %1, 0;\n\t"                     // cnt -= borrow
         GL_PTX_ADD_EPS_MUL_FMA("p0", "p1", "p2")
         "addc.u32 m, 0, 0;\n\t"
         "sub.cc.u32 p0, p0, m;\n\t"
         "subc.u32 p1, p1, 0;\n\t"
         "add.u32 p1, p1, m;\n\t"
         "mov.b64 %0, {p0,p1};\n\t"
-        "}" : "=l"(r), "+r"(bf) : "l"(lo), "l"(hi));
+        "}" : "=l"(r), "+r"(cnt) : "l"(lo), "l"(hi));
     return r;
 #else
-    (void)bf;
-    return gl_reduce128_t<false>(lo, hi);
+    const uint32_t h0 = (uint32_t)hi, h1 = (uint32_t)(hi >> 32);
+    if (lo < h1) cnt--;
+    const gl_t t = lo - h1, u = ((gl_t)h0 << 32) - h0;
+    gl_t r = t + u;
+    if (r < u) r += GL_EPS;
+    return r;
 #endif
 }
+template <bool PRODUCT>
+GL_HD gl_t gl_reduce128_defer_t(gl_t lo, gl_t hi, GlBorrow &bf)
+{
+#if GL_BORROW_MIN
+    uint32_t w;
+    const gl_t r = gl_fold_defer_raw<PRODUCT>(lo, hi, w);
+    gl_borrow_note(bf, w);
+    return r;
+#else
+    return gl_fold_defer_cnt(lo, hi, bf.cnt);
+#endif
+}
+GL_HD gl_t gl_reduce128_defer(gl_t lo, gl_t hi, GlBorrow &bf) { return gl_reduce128_defer_t<true>(lo, hi, bf); }
 
 // MODE 0: p2*EPS as IMAD.LO + IMAD.HI; 1: on the ALU pipe; 2: one IMAD.WIDE (gl_reduce128_wide)
 template <int MODE>
@@ -452,10 +569,24 @@ GL_HD gl_t gl_pow7_m(gl_t x)
     return gl_mul_m<MODE, W4>(x3, x4);
 }
 
-// the same with the rare wrap of every fold deferred into bf (gl_reduce128_defer)
-GL_HD gl_t gl_pow7_defer(gl_t x, uint32_t &bf)
+// the same with the rare wrap of every fold deferred into bf (gl_fold_defer_raw; two folds per flag instruction)
+GL_HD gl_t gl_pow7_defer(gl_t x, GlBorrow &bf)
 {
     gl_t lo, hi;
+#if GL_BORROW_MIN
+    uint32_t wa, wb;
+    gl_sqr_wide(x, lo, hi);
+    const gl_t x2 = gl_fold_defer_raw<true>(lo, hi, wa);
+    gl_mul_wide(x, x2, lo, hi);
+    const gl_t x3 = gl_fold_defer_raw<true>(lo, hi, wb);
+    gl_borrow_note2(bf, wa, wb);
+    gl_sqr_wide(x2, lo, hi);
+    const gl_t x4 = gl_fold_defer_raw<true>(lo, hi, wa);
+    gl_mul_wide(x3, x4, lo, hi);
+    const gl_t x7 = gl_fold_defer_raw<true>(lo, hi, wb);
+    gl_borrow_note2(bf, wa, wb);
+    return x7;
+#else
     gl_sqr_wide(x, lo, hi);
     const gl_t x2 = gl_reduce128_defer(lo, hi, bf);
     gl_mul_wide(x, x2, lo, hi);
@@ -464,6 +595,7 @@ GL_HD gl_t gl_pow7_defer(gl_t x, uint32_t &bf)
     const gl_t x4 = gl_reduce128_defer(lo, hi, bf);
     gl_mul_wide(x3, x4, lo, hi);
     return gl_reduce128_defer(lo, hi, bf);
+#endif
 }
 
 // x^7, the Poseidon S-box (poseidon_goldilocks.hpp:91-97): 4 multiplies

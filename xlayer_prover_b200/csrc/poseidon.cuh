@@ -102,15 +102,15 @@ GL_HD void gl_dot_mac(GlDotAcc &s, gl_t a, gl_t b)
 // DEFER (the leaf hash, POS_DEFER_BORROW): every fold leaves its 2^-33 wrap uncorrected and counts it in bf instead
 // (gl_reduce128_defer); the caller redoes the row with DEFER = false when bf != 0 at the end.
 template <bool DEFER>
-GL_HD gl_t pos_pow7(gl_t x, uint32_t &bf)
+GL_HD gl_t pos_pow7(gl_t x, GlBorrow &bf)
 {
     if (DEFER) return gl_pow7_defer(x, bf);
     return gl_pow7_m<POS_RED_MODE, POS_MUL4W != 0>(x);
 }
 template <bool DEFER, int MODE>
-GL_HD gl_t pos_fold128(gl_t lo, gl_t hi, uint32_t &bf)
+GL_HD gl_t pos_fold128(gl_t lo, gl_t hi, GlBorrow &bf)
 {
-    if (DEFER) return gl_reduce128_defer(lo, hi, bf);
+    if (DEFER) return gl_reduce128_defer_t<false>(lo, hi, bf);   // dot-product accumulators: a general 128-bit value
     return gl_reduce128_m<MODE>(lo, hi);
 }
 
@@ -126,10 +126,10 @@ GL_HD gl_t pos_fold128(gl_t lo, gl_t hi, uint32_t &bf)
 #define POS_DEFER_DOTSUB 1        // deferred rows: the dot-product folds' last subtraction leaves its (2^-28) wrap to the redo as well
 #endif
 #ifndef POS_MDS_FOLD_FMA
-#define POS_MDS_FOLD_FMA 1        // top*EPS of the MDS fold as IMAD + IMAD.HI (6 pipe cycles) instead of four ALU instructions (8)
+#define POS_MDS_FOLD_FMA 2        // top*EPS of the MDS fold: 1 = IMAD + IMAD.HI (6 pipe cycles), 2 = one IMAD.WIDE (EPS from the constant bank), 0 = four ALU instructions (8)
 #endif                            // (each +0.5 % on the leaf hash, profiles/r01_poseidon_defer.txt)
 // r - b for b < 2^40 with the (rare: r < b) wrap left out and counted in bf, like gl_reduce128_defer
-GL_HD gl_t gl_sub_small_defer(gl_t r, gl_t b, uint32_t &bf)
+GL_HD gl_t gl_sub_small_defer(gl_t r, gl_t b, GlBorrow &bf)
 {
 #if GL_DEVICE_PTX
     gl_t o;
@@ -141,15 +141,15 @@ GL_HD gl_t gl_sub_small_defer(gl_t r, gl_t b, uint32_t &bf)
         "subc.cc.u32 a1, a1, b1;\n\t"
         "subc.u32 %1, %1, 0;\n\t"
         "mov.b64 %0, {a0,a1};\n\t"
-        "}" : "=l"(o), "+r"(bf) : "l"(r), "l"(b));
+        "}" : "=l"(o), "+r"(bf.cnt) : "l"(r), "l"(b));
     return o;
 #else
-    (void)bf;
-    return gl_sub(r, b);
+    if (r < b) bf.cnt--;                                          // modelled like the device: counted, value left unfixed
+    return r - b;
 #endif
 }
 template <bool DEFER>
-GL_HD gl_t gl_dot_fold(const GlDotAcc &s, uint32_t &bf)
+GL_HD gl_t gl_dot_fold(const GlDotAcc &s, GlBorrow &bf)
 {
     uint64_t t1 = (uint64_t)s.z1 + s.x0;
     uint64_t t2 = (uint64_t)s.zc + s.x1 + s.y0 + (t1 >> 32);
@@ -164,9 +164,12 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s, uint32_t &bf)
     return gl_sub(r, l4 << 32);
 }
 
+#ifndef POS_MULADD_V2
+#define POS_MULADD_V2 0           // 1: the rank-1 updates of the partial rounds fold with form 2 as well (ptxas then runs out of carry predicates
+#endif                            //    in the partial-round loop and packs them into registers: 548 instead of 388 instructions a round)
 // a*b + c, one fold (c is added into the 128-bit product: (2^64-1)^2 + 2^64 - 1 < 2^128)
 template <bool DEFER>
-GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c, uint32_t &bf)
+GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c, GlBorrow &bf)
 {
     gl_t lo, hi;
     if (POS_MUL4W) gl_mul_wide4(a, b, lo, hi);
@@ -178,7 +181,31 @@ GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c, uint32_t &bf)
     hi += (t < lo);
     lo = t;
 #endif
-    return pos_fold128<DEFER, POS_MULADD_MODE>(lo, hi, bf);
+    if (DEFER) return gl_reduce128_defer_t<POS_MULADD_V2 != 0>(lo, hi, bf);    // a*b + c with b a canonical constant (see gl_fold_defer_raw)
+    return gl_reduce128_m<POS_MULADD_MODE>(lo, hi);
+}
+// two rank-1 updates whose deferred folds share one flag instruction (GL_BORROW_MIN): xa = a*ba + xa, xb = a*bb + xb
+GL_HD void gl_mul_add2_defer(gl_t a, gl_t ba, gl_t bb, gl_t &xa, gl_t &xb, GlBorrow &bf)
+{
+#if GL_BORROW_MIN
+    gl_t lo_a, hi_a, lo_b, hi_b;
+    gl_mul_wide(a, ba, lo_a, hi_a);
+    gl_mul_wide(a, bb, lo_b, hi_b);
+#if GL_DEVICE_PTX
+    asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(lo_a), "+l"(hi_a) : "l"(xa));
+    asm("add.cc.u64 %0, %0, %2;\n\taddc.u64 %1, %1, 0;" : "+l"(lo_b), "+l"(hi_b) : "l"(xb));
+#else
+    gl_t t = lo_a + xa; hi_a += (t < lo_a); lo_a = t;
+    t = lo_b + xb; hi_b += (t < lo_b); lo_b = t;
+#endif
+    uint32_t wa, wb;
+    xa = gl_fold_defer_raw<POS_MULADD_V2 != 0>(lo_a, hi_a, wa);
+    xb = gl_fold_defer_raw<POS_MULADD_V2 != 0>(lo_b, hi_b, wb);
+    gl_borrow_note2(bf, wa, wb);
+#else
+    xa = gl_mul_add<true>(a, ba, xa, bf);
+    xb = gl_mul_add<true>(a, bb, xb, bf);
+#endif
 }
 
 // ---- MDS layer: state' = M^T state,  M[j][i] = circ[(j-i) mod 12] (+8 at i=j=0) ----
@@ -194,7 +221,10 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
         "mov.b64 {h0,h1}, %2;\n\t"
         "add.cc.u32 l1, l1, h0;\n\t"
         "addc.u32 h1, h1, 0;\n\t"
-#if POS_MDS_FOLD_FMA
+#if POS_MDS_FOLD_FMA == 2
+        "mad.lo.cc.u32 l0, h1, %3, l0;\n\t"            // EPS from the constant bank: one IMAD.WIDE with carry-out
+        "madc.hi.cc.u32 l1, h1, %3, l1;\n\t"
+#elif POS_MDS_FOLD_FMA
         GL_PTX_ADD_EPS_MUL_FMA("l0", "l1", "h1")
 #else
         GL_PTX_ADD_EPS_MUL_ALU("l0", "l1", "h1")
@@ -204,7 +234,7 @@ GL_HD gl_t pos_mds_fold(uint64_t L, uint64_t H)
         "subc.u32 l1, l1, 0;\n\t"
         "add.u32 l1, l1, m;\n\t"
         "mov.b64 %0, {l0,l1};\n\t"
-        "}" : "=l"(r) : "l"(L), "l"(H));
+        "}" : "=l"(r) : "l"(L), "l"(H), "r"(GL_EPS_OPAQUE));
     return r;
 #else
     uint64_t lo = L + (H << 32);
@@ -302,9 +332,14 @@ GL_HD void pos_mds_limb(gl_t x[12], const uint32_t *rcl)
 // 2^52 + (half of the folded round constant), and the integer sum is read back from the mantissa: same arithmetic,
 // half the pipe time, and the ALU pipe only sees the fold.  Every intermediate is an integer < 2^53, so the result is
 // exact whatever the rounding mode; the host emulator runs the same expressions in IEEE double.
+#ifndef POS_CVT_I2F
+#define POS_CVT_I2F 1             // 1 = u32 -> double with the conversion instruction instead of the exponent trick + DADD
+#endif
 GL_HD double pos_u32_to_f64(uint32_t v)
 {
-#if GL_DEVICE_PTX
+#if GL_DEVICE_PTX && POS_CVT_I2F
+    return __uint2double_rn(v);                                              // I2F.F64.U32
+#elif GL_DEVICE_PTX
     return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;        // (2^52 + v) - 2^52
 #else
     return (double)v;
@@ -361,6 +396,10 @@ GL_HD void pos_mds_f64(gl_t x[12], const double *rcd)
                                   // unrolled form pushes the kernel past the 32 KB L1.5 instruction cache and costs 4.5 % (profiles/r01_poseidon_variants.txt)
 #endif
 
+#ifndef POS_PRE_UNROLL
+#define POS_PRE_UNROLL 3          // outputs per trip of the rolled pre-matrix loop (1: 22 queue moves per output; 3: 6 per output, +4.5 KB of code)
+#endif
+
 template <bool LOCKSTEP>
 GL_HD void pos_round_sync()
 {
@@ -372,7 +411,7 @@ GL_HD void pos_round_sync()
 // x_i = x_i^7 + rc_i for all 12, as 12/G trips over G lanes with the state rotated by G after each trip
 // (rc == NULL: no constant here, it was folded into the linear layer that follows -- POS_MDS_LIMB)
 template <bool DEFER>
-GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc, uint32_t &bf)
+GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc, GlBorrow &bf)
 {
     constexpr int G = POS_SBOX_GROUP;
     static_assert(12 % G == 0, "POS_SBOX_GROUP must divide 12");
@@ -400,26 +439,34 @@ GL_HD void pos_sbox_layer(gl_t x[12], const gl_t *rc, uint32_t &bf)
 
 // x <- PRE^T x  (the dense pre-multiplied matrix before the partial rounds)
 template <bool DEFER>
-GL_HD void pos_pre_layer(gl_t x[12], uint32_t &bf)
+GL_HD void pos_pre_layer(gl_t x[12], GlBorrow &bf)
 {
 #if POS_ROLL_PRE
     gl_t out[12];
 #pragma unroll
     for (int i = 0; i < 12; i++) out[i] = 0;
+    constexpr int U = POS_PRE_UNROLL;                    // outputs per trip: the 12-word register queue shifts by U per trip
+    static_assert(12 % U == 0, "POS_PRE_UNROLL must divide 12");
 #pragma unroll 1
-    for (int i = 0; i < 12; i++) {
-        const gl_t *col = POS_PRET + 12 * i;
-        GlDotAcc acc;
-        gl_dot_init(acc);
+    for (int i = 0; i < 12; i += U) {
+        gl_t t[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const gl_t *col = POS_PRET + 12 * (i + u);
+            GlDotAcc acc;
+            gl_dot_init(acc);
 #if POS_MDS_LIMB
-        acc.z0 = (uint32_t)POS_MRC[36 + i];
-        acc.z1 = (uint32_t)(POS_MRC[36 + i] >> 32);
+            acc.z0 = (uint32_t)POS_MRC[36 + i + u];
+            acc.z1 = (uint32_t)(POS_MRC[36 + i + u] >> 32);
 #endif
 #pragma unroll
-        for (int j = 0; j < 12; j++) gl_dot_mac(acc, x[j], col[j]);
+            for (int j = 0; j < 12; j++) gl_dot_mac(acc, x[j], col[j]);
+            t[u] = gl_dot_fold<DEFER>(acc, bf);
+        }
 #pragma unroll
-        for (int k = 0; k < 11; k++) out[k] = out[k + 1];
-        out[11] = gl_dot_fold<DEFER>(acc, bf);
+        for (int k = 0; k + U < 12; k++) out[k] = out[k + U];
+#pragma unroll
+        for (int u = 0; u < U; u++) out[12 - U + u] = t[u];
     }
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = out[i];
@@ -443,7 +490,7 @@ GL_HD void pos_pre_layer(gl_t x[12], uint32_t &bf)
 }
 
 template <bool LOCKSTEP, bool DEFER>
-GL_HD void pos_permute_t(gl_t x[12], uint32_t &bf)
+GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf)
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = gl_add_c(x[i], POS_RC[i]);
@@ -479,8 +526,14 @@ GL_HD void pos_permute_t(gl_t x[12], uint32_t &bf)
                 gl_dot_init(acc);
 #pragma unroll
                 for (int i = 0; i < 12; i++) gl_dot_mac(acc, x[i], S[i]);
+                if (DEFER && GL_BORROW_MIN && !POS_MUL4W) {
 #pragma unroll
-                for (int i = 1; i < 12; i++) x[i] = gl_mul_add<DEFER>(x[0], S[11 + i], x[i], bf);
+                    for (int i = 1; i < 11; i += 2) gl_mul_add2_defer(x[0], S[11 + i], S[12 + i], x[i], x[i + 1], bf);
+                    x[11] = gl_mul_add<DEFER>(x[0], S[22], x[11], bf);
+                } else {
+#pragma unroll
+                    for (int i = 1; i < 12; i++) x[i] = gl_mul_add<DEFER>(x[0], S[11 + i], x[i], bf);
+                }
                 x[0] = gl_dot_fold<DEFER>(acc, bf);
             }
         }
@@ -489,6 +542,6 @@ GL_HD void pos_permute_t(gl_t x[12], uint32_t &bf)
 
 GL_HD void pos_permute(gl_t x[12])
 {
-    uint32_t bf = 0;
+    GlBorrow bf = gl_borrow_init();
     pos_permute_t<false, false>(x, bf);
 }

@@ -46,9 +46,13 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 // (every block but the last a multiple of 8 columns); cap_in may alias out.
 // LOCKSTEP: every thread of the CTA runs the same number of permutations (rows past the end are clamped to the
 // last row and simply not stored), so the per-round barriers inside pos_permute_t are reached by all.
-// POS_LEAF_MINBLOCKS (optional): second argument of __launch_bounds__, i.e. a register cap (6 -> 80 registers, 4 -> 128);
-// without it ptxas settles at 96 registers = 5 CTAs of 128 threads per SM
-#ifdef POS_LEAF_MINBLOCKS
+// POS_LEAF_MINBLOCKS: second argument of __launch_bounds__, i.e. a register cap (6 -> 80 registers, 4 -> 128; 0 = none: ptxas then
+// settles at 96 registers = 5 CTAs of 128 threads per SM).  4 lets ptxas take 120 registers: no spills, 16 warps per SM,
+// 1134 against 1124 M perm/s (profiles/r02_pos_variants.txt) -- the kernel does not need the occupancy.
+#ifndef POS_LEAF_MINBLOCKS
+#define POS_LEAF_MINBLOCKS 4
+#endif
+#if POS_LEAF_MINBLOCKS
 #define POS_LEAF_BOUNDS __launch_bounds__(POS_LEAF_BLOCK, POS_LEAF_MINBLOCKS)
 #else
 #define POS_LEAF_BOUNDS __launch_bounds__(POS_LEAF_BLOCK)
@@ -62,14 +66,18 @@ static __device__ __forceinline__ void pos_load8(gl_t v[8], const gl_t *__restri
 #endif
 #if !defined(GLP_EMU)
 static __device__ unsigned long long g_pos_redo_rows;
+#define POS_COUNT_REDO() atomicAdd(&g_pos_redo_rows, 1ull)
+#else
+static unsigned long long g_pos_redo_rows;                       // the emulator's threads are host threads
+#define POS_COUNT_REDO() __atomic_fetch_add(&g_pos_redo_rows, 1ull, __ATOMIC_RELAXED)
 #endif
 
-// the sponge over one row; returns the deferred-wrap count (always 0 when !DEFER)
+// the sponge over one row; returns whether a deferred wrap fired (never when !DEFER)
 template <bool LOCKSTEP, bool DEFER>
-static __device__ __forceinline__ uint32_t pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap)
+static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap)
 {
     gl_t nxt[8];
-    uint32_t bf = 0;
+    GlBorrow bf = gl_borrow_init();
     const uint64_t nblk = (ncols + 7) / 8;
     pos_load8(nxt, p, (uint32_t)(ncols < 8 ? ncols : 8), vec16);
 #pragma unroll
@@ -86,7 +94,7 @@ static __device__ __forceinline__ uint32_t pos_leaf_row(gl_t x[12], const gl_t *
 #pragma unroll
         for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
     }
-    return bf;
+    return DEFER && gl_borrow_hit(bf);
 }
 static __device__ GLP_NOINLINE void pos_leaf_row_exact(gl_t *o, const gl_t *p, uint64_t ncols, int vec16, const gl_t *cap)
 {
@@ -94,9 +102,7 @@ static __device__ GLP_NOINLINE void pos_leaf_row_exact(gl_t *o, const gl_t *p, u
     pos_leaf_row<false, false>(x, p, ncols, vec16 != 0, cap);
 #pragma unroll
     for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
-#if !defined(GLP_EMU)
-    atomicAdd(&g_pos_redo_rows, 1ull);
-#endif
+    POS_COUNT_REDO();
 }
 
 template <bool LOCKSTEP>
@@ -122,7 +128,7 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     }
     const gl_t *cap = cap_in ? cap_in + row * out_pitch : nullptr;
     gl_t x[12];
-    const uint32_t bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap);
+    const bool bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap);
     if (DEFER && bf) {                            // before any store: cap_in may alias out
         pos_leaf_row_exact(o, p, ncols, vec16, cap);
         return;
@@ -144,9 +150,7 @@ static __device__ GLP_NOINLINE void pos_hash_pair_exact(gl_t *dst, const gl_t *s
     pos_permute(x);
 #pragma unroll
     for (int i = 0; i < 4; i++) dst[i] = gl_canon(x[i]);
-#if !defined(GLP_EMU)
-    atomicAdd(&g_pos_redo_rows, 1ull);
-#endif
+    POS_COUNT_REDO();
 }
 static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src)
 {
@@ -155,9 +159,9 @@ static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, con
     for (int i = 0; i < 8; i++) x[i] = src[i];
 #pragma unroll
     for (int i = 8; i < 12; i++) x[i] = 0;
-    uint32_t bf = 0;
+    GlBorrow bf = gl_borrow_init();
     pos_permute_t<false, POS_DEFER_BORROW != 0>(x, bf);
-    if (POS_DEFER_BORROW && bf) {
+    if (POS_DEFER_BORROW && gl_borrow_hit(bf)) {
         pos_hash_pair_exact(dst, src);
         return;
     }
