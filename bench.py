@@ -15,7 +15,8 @@ that the CPU arms -- which run a bounded column sample of the same workload -- a
   value : inputs already resident in HBM, CUDA events on the launching stream, max over ranks.
   e2e   : the same commit through the C ABI with HOST (pinned) buffers: H2D of the trace and D2H of the
           extended matrix + every Merkle node inside the timed region.
-  N > 1 : column-sharded LDE -> one NCCL all-to-all -> row-sharded subtrees -> top levels on rank 0
+  N > 1 : column-sharded LDE whose last NTT pass stores straight into the peers' row slabs over NVLink (the exchange is
+          fused into the transform: no all-to-all) -> row-sharded subtrees -> top levels on rank 0
           (xlayer_prover_b200/sharded.py); total work is fixed, so "scaling": "strong".
 Only the cpu_baseline leg and --impl reference execute anything under oracle/ (as the thing measured there);
 the parity spot-check after the timed region uses it as the checker.
@@ -37,13 +38,24 @@ if ROOT not in sys.path:
 
 P = 0xFFFFFFFF00000001
 SEED = 0x9E3779B97F4A7C15 + 2          # seed = golden ratio + config id
-# Pipe cycles one warp needs for one permutation inside k_linear_hash_rows, from its SASS (tools/sass_mix.py with the loop
-# trip counts 8/7/12/22) and the pipe costs measured on this GPU (profiles/r01_int_pipes.txt: IMAD.WIDE and IMAD.HI 4 cycles
-# per warp instruction per SM sub-partition, other IMAD, DFMA/DADD and every ALU op 2, one issue per cycle).  DFMA shares its
-# dispatch with IMAD.WIDE (DFMA+IMAD.WIDE pairs take 5.5 cycles, 6 if serial), so the multiplier bound counts both.
-# (alu / issue: the SASS count of the exact kernel minus the two ALU instructions the deferred wrap removes from each of the 748 folds)
-POS_PIPE_CYCLES = {"fmaheavy": 25426, "fp64": 4368, "alu": 21712 - 2 * 2 * 748, "issue": 21905 - 2 * 748}
+# One Poseidon permutation, counted two ways.
+# (1) ALGORITHMIC: 1122 field multiplies (118 S-boxes x 4, the 12x12 pre-matrix, 22 partial
+#     rounds x 23) of four 32x32->64 products each, plus the 7 MDS layers' 12 x 12 small-constant products on both 32-bit halves
+#     as DFMA.  Priced at the IMAD.WIDE and DFMA rates glp_measure_pipe_peaks measures in the same run, this is the ceiling
+#     `roofline` reports against: it charges nothing for carries, folds or loads.
+POS_ALG_IMAD_WIDE = 1122 * 4
+POS_ALG_DFMA = 7 * 2 * 144
+# (2) The kernel's own instruction stream (tools/sass_leaf.py on the final binary, profiles/r02_sass_mix_leaf.txt): warp
+#     instructions per permutation by pipe; costs measured in round 1 (profiles/r01_int_pipes.txt): IMAD.WIDE 4 cycles of the
+#     fmaheavy pipe per warp instruction per SM sub-partition, other IMAD, DFMA/I2F and every ALU op 2.  `roofline_sass` is
+#     the multiplier-pipe bound of that stream (how close the kernel runs to its own SASS, not to the algorithm).
+POS_SASS = {"instructions": 18564, "imad_wide": 5096, "imad_other": 948, "fp64": 2304, "alu": 8852}
+POS_PIPE_CYCLES = {"fmaheavy": 4 * POS_SASS["imad_wide"] + 2 * POS_SASS["imad_other"], "fp64": 2 * POS_SASS["fp64"],
+                   "alu": 2 * POS_SASS["alu"], "issue": POS_SASS["instructions"]}
 POS_BOUND_CYCLES = POS_PIPE_CYCLES["fmaheavy"] + POS_PIPE_CYCLES["fp64"]
+# root of the default workload (2^23 x 660, blowup 2, SEED): the N = 1 run checks it against the reference build through
+# whole columns and Merkle paths (verify), every N compares its root with it (verify.root_equals_n1)
+KNOWN_ROOTS = {(23, 660, 1): [0x2954300a93d8e1ed, 0xb89e6e7f7a6d3906, 0x8e88252716f12068, 0xc8cda114b642004f]}
 # dram__bytes_read.sum + dram__bytes_write.sum of k_linear_hash_rows from the ncu --set full capture at 2^19 rows x 660
 # columns (profiles/r01_ncu_full_summary_final2.txt, final binary of round 1: 2.834834 GB + 33.56 MB), per row; a launch's
 # traffic scales with its rows
@@ -62,7 +74,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
-    ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="target seconds of CPU work for the cpu_baseline sample")
+    ap.add_argument("--cpu-budget-s", type=float, default=25.0, help="target seconds of CPU work for the cpu_baseline sample")
     return ap.parse_args()
 
 
@@ -138,76 +150,86 @@ def cpu_oracle():
     return refbind.port(), "port"
 
 
-def cpu_sample_cols(orc, log_rows, log_blowup, ncols, budget_s, nsteps):
-    """Pick the column count of the bounded CPU sample: calibrate on 2^16 rows, predict 2^log_rows."""
-    from xlayer_prover_b200._capi import synth_matrix
-    n0 = 1 << 16
-    a = synth_matrix(n0, 16, SEED)
-    orc.commit(a, n0 << log_blowup)                                   # warm caches / thread pool
-    _, _, (t_lde, t_mt) = orc.commit(a, n0 << log_blowup)
-    n = 1 << log_rows
-    scale = (n / n0)
-    lde_per_col = t_lde / 16 * scale * (log_rows + 1.0) / 17.0        # ~ N log N
-    perm_s = t_mt / perms_per_commit(n0 << log_blowup, 16)
-    try:
-        import psutil
-        avail = psutil.virtual_memory().available
-    except Exception:
-        avail = 32 << 30
-    best = 8
-    for c in (8, 16, 32, 64, 128, 256, 512):
-        if c > ncols:
-            break
-        est = lde_per_col * c + perm_s * perms_per_commit(n << log_blowup, c)
-        mem = 8 * n * c * (1 + 2 * (1 << log_blowup)) + 32 * (2 * (n << log_blowup))
-        if est * nsteps <= budget_s and mem <= 0.5 * avail:
-            best = c
-    return best
+CPU_SAMPLE_COLS = 64                     # the CPU arms time C' = 64 of the C columns at the full 2^23 rows
 
 
-def cpu_commit_step(orc, a, n_ext):
-    t0 = time.perf_counter()
-    _, tree, (t_lde, t_mt) = orc.commit(a, n_ext)
-    return time.perf_counter() - t0, t_lde, t_mt, tree
+_HOST_CORES = None
+
+
+def host_cores():
+    """CPUs this process may run on, read once: with OMP_PROC_BIND set libgomp pins the main thread to one place when it
+    starts, after which sched_getaffinity of the main thread says 1."""
+    global _HOST_CORES
+    if _HOST_CORES is None:
+        try:
+            _HOST_CORES = len(os.sched_getaffinity(0))
+        except Exception:
+            _HOST_CORES = os.cpu_count() or 1
+    return _HOST_CORES
 
 
 def run_cpu_baseline(args, budget_s, nsteps=1, warmup=0):
-    """Times the oracle (oracle/_ref when the reference compiled, else the C port) on 2^log_rows rows x C' columns."""
+    """Times the reference's own CPU code (oracle/_ref when it compiled here, else the C port) on a bounded sample of the
+    workload and extrapolates to the full job, component by component:
+        extendPol      on C' = 64 of the C columns at the full N rows            -> t_lde,    linear in columns
+        merkletree     of the first R' rows x C' columns of that extension       -> t_tree   (leaf hashes + levels of R' leaves)
+        merkletree     of R' rows x 4 columns (leaves copied: the level loop)    -> t_lev
+        t_full = t_lde * C/C' + (t_tree - t_lev) * (N_ext/R') * ceil(C/8)/ceil(C'/8) + t_lev * (N_ext - 1)/(R' - 1)
+    The tree levels are NOT scaled by the column count (they do not depend on it), and rows are independent, so both
+    scalings are exact in the permutation count; the LDE is linear in columns at >= 32 columns on these hosts."""
     from xlayer_prover_b200._capi import synth_matrix
     orc, kind = cpu_oracle()
-    cores = orc.max_threads()
+    cores = host_cores()
+    orc.set_threads(cores)                # torch.distributed.run exports OMP_NUM_THREADS=1; the reference arm uses every core it may
     n, n_ext = 1 << args.log_rows, 1 << (args.log_rows + args.log_blowup)
-    c = cpu_sample_cols(orc, args.log_rows, args.log_blowup, args.cols, budget_s, nsteps + warmup)
-    a = synth_matrix(n, c, SEED, ncols_total=args.cols)
-    for _ in range(warmup):
-        cpu_commit_step(orc, a, n_ext)
-    times, lde, mt = [], [], []
-    for _ in range(nsteps):
-        t, tl, tm, _ = cpu_commit_step(orc, a, n_ext)
-        times.append(t)
-        lde.append(tl)
-        mt.append(tm)
-    t = (sum(lde) + sum(mt)) / len(times)        # the reference's own two calls; numpy buffer allocation excluded
-    # the reference's AVX-512 build on the same sample, when the host has the instructions (SURVEY 8d: "also reported");
-    # the headline CPU number stays the AVX2 build, the reference's default (Makefile:19)
-    avx512 = None
-    try:
-        from oracle import refbind
-        has512 = any("avx512f" in l for l in open("/proc/cpuinfo") if l.startswith("flags"))
-        o512 = refbind.reference(avx512=True) if (kind == "reference" and has512) else None
-        if o512 is not None:
-            _, tl, tm, _ = cpu_commit_step(o512, a, n_ext)
-            avx512 = {"value": n * c / (tl + tm) / 1e6, "unit": "Melem/s", "extendPol_s": tl, "merkletree_s": tm}
-    except Exception as ex:                                              # a baseline extra must never take the bench down
-        avx512 = {"error": repr(ex)}
+    C, c = args.cols, min(CPU_SAMPLE_COLS, args.cols)
+    a = synth_matrix(n, c, SEED, ncols_total=C)
+    # calibrate the leaf sample on 2^14 rows: permutations/s of this host
+    cal_rows = min(n_ext, 1 << 14)
+    t0 = time.perf_counter()
+    orc.merkletree(np.ascontiguousarray(np.resize(a, (cal_rows, c))))
+    perm_s = (cal_rows * ((c + 7) // 8) + cal_rows) / max(1e-6, time.perf_counter() - t0)
+    per_step = budget_s / max(1, nsteps + warmup)
+    lde_est = 0.083 * c * (16.0 / cores) * (n / float(1 << 23))           # round-1 record: 0.083 s per column at 2^23 rows on 16 cores
+    leaf_budget = max(0.4, per_step - lde_est)
+    leaf_rows = 1 << 12
+    while leaf_rows * 2 <= n_ext and (2 * leaf_rows) * ((c + 7) // 8 + 2) / perm_s <= leaf_budget:
+        leaf_rows *= 2
+    leaf_rows = min(leaf_rows, n_ext)
+    steps = []
+    for i in range(warmup + nsteps):
+        t = orc.timed_parts(a, n_ext, leaf_rows)
+        if i >= warmup:
+            steps.append(t)
+    t_lde, t_tree, t_lev = (sum(x[k] for x in steps) / len(steps) for k in range(3))
+    t_leaf = max(0.0, t_tree - t_lev)
+    pc, pC = (c + 7) // 8, (C + 7) // 8
+    full_lde = t_lde * C / c
+    full_leaf = t_leaf * (n_ext / leaf_rows) * (pC / pc if c > 4 else 0)
+    full_lev = t_lev * (n_ext - 1) / max(1, leaf_rows - 1)
+    t_full = full_lde + full_leaf + full_lev
     return {
-        "avx512_build": avx512,
-        "value": n * c / t / 1e6, "unit": "Melem/s", "cores": cores, "kind": kind,
-        "sample": "2^%d rows x %d of %d columns, blowup %d, %d timed step(s); extendPol %.2f s + merkletree %.2f s per step"
-                  % (args.log_rows, c, args.cols, 1 << args.log_blowup, nsteps, sum(lde) / len(lde), sum(mt) / len(mt)),
-        "seconds_per_step": t, "sample_cols": c,
-        "poseidon_hash_per_s": perms_per_commit(n_ext, c) / (sum(mt) / len(mt)),
+        "value": n * C / t_full / 1e6, "unit": "Melem/s", "cores": cores, "kind": kind, "extrapolated": True,
+        "sample": "per step: extendPol of 2^%d rows x %d of %d columns (blowup %d), merkletree of the first 2^%d of its 2^%d rows, "
+                  "level loop of 2^%d leaves; measured %.2f + %.2f + %.2f s, extrapolated to the full job %.1f + %.1f + %.1f s "
+                  "(columns, permutations, nodes; %d timed step(s))"
+                  % (args.log_rows, c, C, 1 << args.log_blowup, leaf_rows.bit_length() - 1, args.log_rows + args.log_blowup,
+                     leaf_rows.bit_length() - 1, t_lde, t_tree, t_lev, full_lde, full_leaf, full_lev, len(steps)),
+        "seconds_per_step_measured": t_lde + t_tree + t_lev, "seconds_full_job": t_full, "sample_cols": c, "sample_leaf_rows": leaf_rows,
+        "full_job_seconds": {"extendPol": full_lde, "leaf_hash": full_leaf, "tree_levels": full_lev},
+        "poseidon_hash_per_s": (leaf_rows * pc + leaf_rows - 1) / t_tree if t_tree > 0 else None,
+        "omp": {"threads": cores, "OMP_PROC_BIND": os.environ.get("OMP_PROC_BIND"), "build": "AVX2" if kind == "reference" else "scalar C"},
     }
+
+
+def workload_config(args):
+    """`config` is the same object in both arms (the driver compares them)."""
+    return {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
+                        % (args.log_rows, args.cols, args.log_rows + args.log_blowup),
+            "l2_policy": "inputs (%.1f GB) far larger than the 126 MB L2; no flush needed" % (8.0 * (1 << args.log_rows) * args.cols / 1e9),
+            "seed": hex(SEED),
+            "cpu_sample": "the CPU arms time %d of the %d columns at the full row count and extrapolate by component (cpu_baseline.sample)"
+                          % (min(CPU_SAMPLE_COLS, args.cols), args.cols)}
 
 
 def main_reference(args):
@@ -215,17 +237,15 @@ def main_reference(args):
     if rank != 0:
         return 0
     base = run_cpu_baseline(args, budget_s=150.0, nsteps=max(1, args.steps), warmup=max(0, min(args.warmup, 1)))
+    keys = ("value", "unit", "cores", "kind", "sample", "extrapolated", "full_job_seconds", "omp")
     line = {
         "impl": "reference", "metric": "LDE+Merkle commit throughput (2^%d x %d, blowup %d)" % (args.log_rows, args.cols, 1 << args.log_blowup),
         "value": base["value"], "unit": "Melem/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": base["seconds_per_step"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "u64", "data": "synthetic",
-        "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
-                               % (args.log_rows, args.cols, args.log_rows + args.log_blowup),
-                   "parallelism": "host CPU, OpenMP x%d" % base["cores"], "seed": hex(SEED),
-                   "cpu_sample": "every step times %d of the %d columns at the full 2^%d rows (both stages are linear in the column count)"
-                                 % (base["sample_cols"], args.cols, args.log_rows)},
-        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "avx512_build")},
+        "ms_per_step": base["seconds_full_job"] * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u64", "data": "synthetic", "extrapolated": True,
+        "config": workload_config(args),
+        "parallelism": "host CPU, OpenMP x%d" % base["cores"],
+        "cpu_baseline": {k: base[k] for k in keys},
         "e2e": {"value": base["value"], "unit": "Melem/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "poseidon_hash_per_s": base["poseidon_hash_per_s"], "gpu_launches": 0,
     }
@@ -300,7 +320,7 @@ def main_ours(args):
     stream = torch.cuda.Stream(device=dev)
     ctx.set_stream(stream.cuda_stream)
     hbm_peak, peak_src = measured_peaks()
-    int_peak = ctx.measure_int_peak()
+    int_peak = ctx.measure_pipe_peaks()
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -329,6 +349,7 @@ def main_ours(args):
         ctx.get_profile()
         barrier()
         launches0 = ctx.launch_count()
+        retries0, redo0 = ctx.ntt_retry_count(), ctx.leaf_redo_rows()
         ctx.set_profiling(True)
         sampler = ClockSampler(local_rank)
         sampler.start()
@@ -343,11 +364,12 @@ def main_ours(args):
         ctx.set_profiling(False)
         prof = ctx.get_profile()
         launches = ctx.launch_count() - launches0
+        retries, redo = ctx.ntt_retry_count() - retries0, ctx.leaf_redo_rows() - redo0
         ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         ms_per_step = float(ms.item()) / K
-        result.update(ms_per_step=ms_per_step, launches=launches, prof=prof, clocks=clocks,
+        result.update(ms_per_step=ms_per_step, launches=launches, prof=prof, clocks=clocks, retries=retries, redo=redo,
                       root=[int(x) for x in (root.cpu().numpy().view(np.uint64) if hasattr(root, "cpu") else root)] if root is not None else None)
 
         # ---- parity spot-check at full size (untimed) ----
@@ -357,7 +379,10 @@ def main_ours(args):
                 if sc is None:
                     verify = verify_full_size(ctx, torch, dext, dtree, n, n_ext, C, 0, C, 0, n_ext)
                 else:
-                    verify = {"note": "N>1: root compared with the N=1 root by the caller; tree assembled on rank 0"}
+                    verify = {"note": "N > 1: the tree is assembled on rank 0; slabs and nodes are compared with the N = 1 result by tests/test_gpu_parity.py::test_sharded_commit_two_gpus"}
+                known = KNOWN_ROOTS.get((args.log_rows, C, args.log_blowup))
+                verify["root_equals_n1"] = (result["root"] == known) if (known and result["root"]) else None
+                verify["root_n1_source"] = "committed root of the N = 1 run of this workload (bench.py KNOWN_ROOTS), itself checked against the reference build at N = 1" if known else "no committed root for this shape"
             except Exception as ex:                                     # never let the checker hide the measurement
                 verify = {"error": repr(ex)}
         result["verify"] = verify
@@ -387,6 +412,9 @@ def main_ours(args):
         leaf_bytes = 8.0 * C * R + 32.0 * R                              # algorithmic bytes of one leaf-hash launch
         leaf_gbs = leaf_bytes / (leaf_ms * 1e-3) / 1e9 if leaf_ms > 0 else None
         leaf_perms = R * ((C + 7) // 8)
+        leaf_pps = leaf_perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None
+        clk_hz = (result["clocks"].get("sm_mhz") or 1965.0) * 1e6
+        alg_peak = 1.0 / (POS_ALG_IMAD_WIDE / int_peak["imad_wide_lane_ops_per_s"] + POS_ALG_DFMA / int_peak["dfma_lane_ops_per_s"])
         lde_ms = (prof["intt"][0] + prof["ntt_ext"][0]) / K
         wcols = w
         lde_bytes = 8.0 * wcols * (n + n_ext)
@@ -395,30 +423,39 @@ def main_ours(args):
             "value": n * C / sec / 1e6, "unit": "Melem/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": result["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": "zkEVM batch-proof stage-1 commit: 2^%d rows x %d cols -> 2^%d rows, extendPol + MerkleTreeGL (BASELINE.json configs[1])"
-                                   % (args.log_rows, C, args.log_rows + args.log_blowup),
-                       "l2_policy": "inputs (%.1f GB) far larger than the 126 MB L2; no flush needed" % (8.0 * n * C / 1e9),
-                       "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d whose last NTT pass stores into the peers' row slabs over NVLink (fused exchange) -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
-                       "seed": hex(SEED)},
+            "config": workload_config(args),
+            "parallelism": "single GPU" if world == 1 else "column-sharded LDE x%d whose last NTT pass stores into the peers' row slabs over NVLink (fused exchange) -> row-sharded Merkle, top %d levels on rank 0" % (world, world.bit_length() - 1),
             "commit_ms": result["ms_per_step"], "poseidon_hash_per_s": perms / sec,
             "leaf_hash_rows_per_s": (R / (leaf_ms * 1e-3)) if leaf_ms > 0 else None,
             "stage_ms": {"intt": prof["intt"][0] / K, "ntt_ext": prof["ntt_ext"][0] / K, "leaf_hash": prof["leaf_hash"][0] / K,
                          "tree_levels": prof["tree_levels"][0] / K, "note": "rank 0, per step, CUDA events on the launching stream"},
-            "roofline": {"kernel": "k_linear_hash_rows", "bound": "hbm", "achieved": leaf_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": (leaf_gbs / hbm_peak) if leaf_gbs else None,
+            "ntt_retries": result["retries"], "leaf_redo_rows": result["redo"],
+            "roofline": {"kernel": "k_linear_hash_rows", "bound": "int", "achieved": leaf_pps, "peak": alg_peak,
+                         "unit": "Poseidon permutations/s", "frac": (leaf_pps / alg_peak) if (leaf_pps and alg_peak) else None,
                          "traffic": LEAF_DRAM_BYTES_PER_ROW_660 * R if C == 660 else None,
-                         "traffic_note": "ncu dram bytes per launch, scaled from the 2^19-row capture by rows (3.0 % over the algorithmic bytes)" if C == 660 else None,
-                         "peak_source": peak_src,
-                         "launch_ms": leaf_ms, "algorithmic_bytes_per_launch": leaf_bytes,
-                         "note": "dominant kernel by time; it is integer-issue bound, not HBM bound -- see roofline_int"},
-            "roofline_int": {"kernel": "k_linear_hash_rows", "bound": "integer multiplier pipes (fmaheavy IMAD.WIDE + FP64 DFMA)",
-                             "achieved": leaf_perms / (leaf_ms * 1e-3) if leaf_ms > 0 else None,
-                             "peak": 148 * 4 * 32 * (result["clocks"].get("sm_mhz") or 1965.0) * 1e6 / POS_BOUND_CYCLES,
-                             "unit": "Poseidon permutations/s",
-                             "frac": (leaf_perms / (leaf_ms * 1e-3)) / (148 * 4 * 32 * (result["clocks"].get("sm_mhz") or 1965.0) * 1e6 / POS_BOUND_CYCLES) if leaf_ms > 0 else None,
-                             "pipe_cycles_per_warp_permutation": POS_PIPE_CYCLES, "measured_lane_ops_per_s": int_peak,
-                             "note": "peak = 148 SMs x 4 sub-partitions x 32 lanes x SM clock / multiplier-pipe cycles per warp-permutation; "
-                                     "ncu (profiles/r01_ncu_full_summary_call7.txt): fmaheavy 68 % busy, ALU 59 %, FP64 12 %, issue 60 %"},
+                         "traffic_note": "ncu dram bytes per launch, scaled from the 2^19-row capture by rows (3.0 % over the algorithmic bytes 8*C + 32 per row)" if C == 660 else None,
+                         "launch_ms": leaf_ms, "permutations_per_launch": leaf_perms,
+                         "peak_source": "algorithmic integer ceiling: %d IMAD.WIDE + %d DFMA lane-instructions per permutation at the rates "
+                                        "glp_measure_pipe_peaks measured in this run (%.3g and %.3g lane-ops/s)"
+                                        % (POS_ALG_IMAD_WIDE, POS_ALG_DFMA, int_peak["imad_wide_lane_ops_per_s"], int_peak["dfma_lane_ops_per_s"]),
+                         "note": "dominant kernel by time (%.0f %% of the step); integer work, not HBM: see roofline_hbm for the byte figure and "
+                                 "roofline_sass / roofline_issue for how close the kernel runs to its own instruction stream"
+                                 % (100.0 * (prof["leaf_hash"][0] / K) / result["ms_per_step"])},
+            "roofline_hbm": {"kernel": "k_linear_hash_rows", "bound": "hbm", "achieved": leaf_gbs, "peak": hbm_peak, "unit": "GB/s",
+                             "frac": (leaf_gbs / hbm_peak) if leaf_gbs else None, "peak_source": peak_src,
+                             "algorithmic_bytes_per_launch": leaf_bytes},
+            "roofline_sass": {"kernel": "k_linear_hash_rows", "bound": "multiplier pipes of the kernel's own SASS (fmaheavy IMAD + FP64)",
+                              "achieved": leaf_pps, "peak": 148 * 4 * 32 * clk_hz / POS_BOUND_CYCLES, "unit": "Poseidon permutations/s",
+                              "frac": leaf_pps / (148 * 4 * 32 * clk_hz / POS_BOUND_CYCLES) if leaf_pps else None,
+                              "pipe_cycles_per_warp_permutation": POS_PIPE_CYCLES, "sass_instructions_per_permutation": POS_SASS,
+                              "source": "tools/sass_leaf.py on the shipped binary (profiles/r02_sass_mix_leaf.txt)"},
+            "roofline_issue": {"kernel": "k_linear_hash_rows", "bound": "mixed integer issue rate (IMAD + IADD3 interleaved, measured in this run)",
+                               "achieved": leaf_pps * POS_SASS["instructions"] if leaf_pps else None,
+                               "peak": int_peak["interleaved_lane_ops_per_s"], "unit": "lane-instructions/s",
+                               "frac": leaf_pps * POS_SASS["instructions"] / int_peak["interleaved_lane_ops_per_s"] if leaf_pps else None,
+                               "note": "the B200 issues ~70 integer lane-instructions per clock per SM whatever the IMAD/ALU mix (IMAD alone 60, IADD3 alone 61, "
+                                       "interleaved 70): the kernel's stream runs at that rate, so only a shorter stream makes it faster"},
+            "measured_lane_ops_per_s": int_peak,
             "roofline_lde": {"kernels": "k_ntt_pass: 3 INTT + 3 NTT tile passes per column block", "bound": "hbm", "achieved": lde_bytes / (lde_ms * 1e-3) / 1e9 if lde_ms > 0 else None,
                              "peak": hbm_peak, "unit": "GB/s", "frac": (lde_bytes / (lde_ms * 1e-3) / 1e9 / hbm_peak) if lde_ms > 0 else None,
                              "algorithmic_bytes": lde_bytes, "design_traffic_bytes": 8.0 * wcols * (5 * n + 3 * n_ext), "lde_ms": lde_ms},
@@ -428,7 +465,7 @@ def main_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             try:
                 base = run_cpu_baseline(args, args.cpu_budget_s)
-                line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "avx512_build")}
+                line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample", "extrapolated", "full_job_seconds", "omp")}
             except Exception as ex:
                 line["cpu_baseline"] = {"error": repr(ex)}
         emit(line)
@@ -530,6 +567,12 @@ def emit(line):
 
 def main():
     args = parse_args()
+    host_cores()
+    if args.impl == "reference":
+        # before libgomp initialises: every core the process may use, threads spread over them.
+        # torch.distributed.run exports OMP_NUM_THREADS=1 for its workers; rank 0 of the reference arm is the only worker.
+        os.environ["OMP_NUM_THREADS"] = str(host_cores())
+        os.environ.setdefault("OMP_PROC_BIND", "spread")
     quiet_stdout()
     if args.impl == "reference":
         return main_reference(args)

@@ -10,6 +10,7 @@
 #include "glprover.h"
 #include <stdexcept>
 #include <string>
+#include <vector>
 #include <cstdlib>
 
 namespace glp
@@ -19,6 +20,29 @@ namespace glp
     {
         const char *d = std::getenv("GLP_DEVICE");
         return d ? std::atoi(d) : 0;
+    }
+
+    // devices used by extendPol / merkelize: GLP_DEVICES="0,1,2,3" (a power-of-two count; the work is split over them,
+    // include/glprover.h glp_multi_*), else the single device above
+    inline std::vector<int> device_list()
+    {
+        std::vector<int> d;
+        if (const char *e = std::getenv("GLP_DEVICES"))
+        {
+            const char *p = e;
+            while (*p)
+            {
+                char *end = nullptr;
+                const long v = std::strtol(p, &end, 10);
+                if (end == p)
+                    break;
+                d.push_back((int)v);
+                p = (*end == ',') ? end + 1 : end;
+            }
+        }
+        if (d.empty())
+            d.push_back(default_device());
+        return d;
     }
 
     [[noreturn]] inline void raise(int rc, const char *where)
@@ -51,8 +75,36 @@ namespace glp
     {
         static thread_local ThreadCtx t;
         if (!t.ctx)
-            check(glp_init(default_device(), &t.ctx), "glp_init");
+            check(glp_init(device_list()[0], &t.ctx), "glp_init");
         return t.ctx;
+    }
+
+    // GLP_DEVICES names more than one device: the big host-to-host calls (extendPol, merkelize) go through a glp_multi.
+    // One per calling thread, created on first use -- Starks::genProof makes those calls from its main thread only
+    // (src/starkpil/starks.cpp:53-57), the per-thread objects of friProve.cpp keep the single-device context above.
+    inline bool multi_enabled()
+    {
+        static const bool on = device_list().size() > 1;
+        return on;
+    }
+    struct ThreadMulti
+    {
+        glp_multi *m = nullptr;
+        ~ThreadMulti()
+        {
+            if (m)
+                glp_multi_destroy(m);
+        }
+    };
+    inline glp_multi *thread_multi()
+    {
+        static thread_local ThreadMulti t;
+        if (!t.m)
+        {
+            const std::vector<int> d = device_list();
+            check(glp_multi_init((int)d.size(), d.data(), &t.m), "glp_multi_init");
+        }
+        return t.m;
     }
 } // namespace glp
 #endif

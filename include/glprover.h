@@ -74,6 +74,11 @@ int glp_mem_info(glp_ctx *ctx, uint64_t *free_bytes, uint64_t *total_bytes);
  * size must be a power of two <= 2^32; size == 0 or ncols == 0 is a no-op; dst == NULL or dst == src works
  * in place.  The reference's buffer/nphase/nblock arguments are performance hints and have no equivalent. */
 int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend);
+/* The same with rows >= live_rows of src READ AS ZERO (never loaded): what a transform through an NTT_Goldilocks object
+ * built with extension > 1 computes, whose reversePermutation zero-fills every row whose source index is >= size/extension
+ * (ntt_goldilocks.cpp:259-277).  live_rows >= size is glp_ntt. */
+int glp_ntt_live(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend,
+                 uint64_t live_rows);
 /* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352): out[i,c] = P_c(shift * w_ext^i), i < n_ext, where
  * P_c interpolates in[:,c] on the size-n subgroup.  out may alias in. */
 int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
@@ -132,6 +137,12 @@ uint64_t glp_tree_num_elements(uint64_t nrows);
  * the sibling path; proof has width + 4*ceil(log2 height) words.  source / nodes may live on the device. */
 int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source, const uint64_t *nodes,
                            uint64_t width, uint64_t height, uint64_t idx);
+/* The same for a batch of indices, in one launch and one download: proofs[q * (width + 4*ceil(log2 height)) ...] =
+ * getGroupProof(idx[q]), q < nidx.  This is the FRI query phase's access pattern (src/starkpil/fri/friProve.cpp:150-170,
+ * 219-250: every tree is asked for every query index); with source and nodes on the device only the proofs cross the link.
+ * idx is a host array; source and nodes are both device or both host memory; proofs may be either when they are device. */
+int glp_merkle_group_proofs(glp_ctx *ctx, uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width,
+                            uint64_t height, const uint64_t *idx, uint64_t nidx);
 
 /* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
  * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip
@@ -140,6 +151,29 @@ int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source
  * upload of block k+1, LDE + sponge absorption of block k and download of block k-1 overlap on three streams. */
 int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
                uint64_t n, uint64_t n_ext, uint64_t ncols);
+
+/* ---- several GPUs, one process (SURVEY 8e behind the C ABI) ----
+ * The reference's prover is one C++ process (Starks::genProof, src/starkpil/starks.cpp:53-57,134-138,215-219); a glp_multi
+ * drives G = 2^k devices from it.  glp_multi_init creates one glp_ctx per device and enables peer access between all of
+ * them (NVLink/NVSwitch).  Every call below takes HOST pointers (pinned memory copies fastest) and returns when the
+ * results are in them; work is split exactly as in the one-process-per-GPU path (xlayer_prover_b200/sharded.py):
+ * columns of the trace for the LDE, rows of the extension for the tree, the exchange in between fused into the LDE's
+ * last NTT pass as stores into the owning device's row slab, the top log2(G) tree levels on the first device.
+ * Results are bit-identical for every G.  devs == NULL means devices 0..ndev-1; listing ONE device ndev times is allowed
+ * (testing on a one-GPU box).  Shapes too small to split (fewer than 8 columns or 2 rows per device), and calls handed a
+ * device pointer (device-resident data belongs to one device), run on the first device's context. */
+typedef struct glp_multi glp_multi;
+int glp_multi_init(int ndev, const int *devs, glp_multi **m);
+void glp_multi_destroy(glp_multi *m);
+int glp_multi_device_count(const glp_multi *m);
+glp_ctx *glp_multi_ctx(glp_multi *m, int i);            /* the i-th device's context (owned by m) */
+/* NTT_Goldilocks::extendPol (ntt_goldilocks.cpp:326-352), column-sharded: device g extends columns [c_g, c_{g+1}). */
+int glp_multi_extend_pol(glp_multi *m, uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
+/* PoseidonGoldilocks::merkletree (poseidon_goldilocks.cpp:266-301), row-sharded: device g hashes rows [g R, (g+1) R). */
+int glp_multi_merkletree(glp_multi *m, uint64_t *tree, const uint64_t *in, uint64_t ncols, uint64_t nrows, uint64_t dim);
+/* glp_commit on G devices: extendPol + merkletree with the extension exchanged over NVLink inside the LDE. */
+int glp_multi_commit(glp_multi *m, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in, uint64_t n,
+                     uint64_t n_ext, uint64_t ncols);
 
 /* ---- the callers either side of the commit ---- */
 /* Step 4 of Starks::genProof, the quotient commit (src/starkpil/starks.cpp:261-291):
@@ -169,6 +203,9 @@ int glp_fri_group_tree(glp_ctx *ctx, uint64_t *aux, uint64_t *tree, uint64_t roo
 /* dst[i*ncols + c] = splitmix64(seed ^ ((row0+i)*ncols_total + col0 + c)) mod p, generated on the device */
 int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols, uint64_t row0, uint64_t col0,
                    uint64_t ncols_total, uint64_t seed);
+/* dst[j*ncols + i] = (i+1) * F_j mod p, F_0 = F_1 = 1, F_j = F_(j-2) + F_(j-1): the Fibonacci matrix of the reference's Merkle
+ * benchmark and tests (src/goldilocks/benchs/bench.cpp:410-427), generated on the device */
+int glp_fib_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols);
 /* out[0] = sum of all words mod p, out[1] = sum of word_i * (i+1) mod p  (order-sensitive checksum) */
 int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2]);
 /* exercises every device field primitive (PTX paths) on n pseudo-random + edge operands and returns the

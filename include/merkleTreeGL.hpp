@@ -81,7 +81,10 @@ public:
     {
         if (height == 0)
             return;
-        glp::check(glp_merkletree(glp::thread_ctx(), raw(nodes), raw(source), width, height, 1), "MerkleTreeGL::merkelize");
+        if (glp::multi_enabled()) // GLP_DEVICES: leaf rows split over the devices, top levels on the first (glp_multi_merkletree)
+            glp::check(glp_multi_merkletree(glp::thread_multi(), raw(nodes), raw(source), width, height, 1), "MerkleTreeGL::merkelize");
+        else
+            glp::check(glp_merkletree(glp::thread_ctx(), raw(nodes), raw(source), width, height, 1), "MerkleTreeGL::merkelize");
     }
 
     uint64_t getTreeNumElements() { return glp_tree_num_elements(height); } // (2*height - 1) * HASH_SIZE (hpp:59-62)

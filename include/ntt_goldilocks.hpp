@@ -82,7 +82,12 @@ public:
         (void)nblock;
         if (ncols == 0 || size == 0)
             return; // ntt_goldilocks.cpp:168-171
-        glp::check(glp_ntt(glp::thread_ctx(), raw(dst), raw(src), size, ncols, inverse ? 1 : 0, extend ? 1 : 0), "NTT_Goldilocks::NTT");
+        // an object built with extension > 1 reads rows >= size/extension as zero (reversePermutation's zero-fill,
+        // ntt_goldilocks.cpp:259-277); in place that combination asserts in the reference (:301-304)
+        const uint64_t live = extension > 1 ? size / (uint64_t)extension : size;
+        if (extension > 1 && (dst == src || dst == NULL))
+            throw std::invalid_argument("NTT_Goldilocks::NTT: in place with extension > 1 is not implemented (ntt_goldilocks.cpp:301-304)");
+        glp::check(glp_ntt_live(glp::thread_ctx(), raw(dst), raw(src), size, ncols, inverse ? 1 : 0, extend ? 1 : 0, live), "NTT_Goldilocks::NTT");
     }
 
     void INTT(Goldilocks::Element *dst, Goldilocks::Element *src, u_int64_t size, u_int64_t ncols = 1, Goldilocks::Element *buffer = NULL,
@@ -125,7 +130,10 @@ public:
         (void)buffer;
         (void)nphase;
         (void)nblock;
-        glp::check(glp_extend_pol(glp::thread_ctx(), raw(output), raw(input), N_Extended, N, ncols), "NTT_Goldilocks::extendPol");
+        if (glp::multi_enabled())
+            glp::check(glp_multi_extend_pol(glp::thread_multi(), raw(output), raw(input), N_Extended, N, ncols), "NTT_Goldilocks::extendPol");
+        else
+            glp::check(glp_extend_pol(glp::thread_ctx(), raw(output), raw(input), N_Extended, N, ncols), "NTT_Goldilocks::extendPol");
     }
 };
 

@@ -136,6 +136,33 @@ class _Lib:
         return out, tree, (secs[0], secs[1])
 
 
+    def timed_parts(self, inp, n_ext, leaf_rows):
+        """The three pieces bench.py's CPU arm times, each one call of the library's own entry point on preallocated
+        buffers (perf_counter around the foreign call): extendPol of `inp` to n_ext rows; merkletree of the first
+        `leaf_rows` rows of the extension (leaf hashes + the levels above them); merkletree of a 4-column matrix of
+        `leaf_rows` rows (<= 4 columns are copied into the leaves unhashed, so this is the level loop alone).
+        Returns (t_extend_pol, t_tree_sample, t_levels_sample)."""
+        import time
+        inp = np.ascontiguousarray(inp, dtype=np.uint64)
+        n, ncols = inp.shape
+        out = np.zeros((n_ext, ncols), dtype=np.uint64)
+        buf = np.zeros((n_ext, ncols), dtype=np.uint64)
+        src = inp.copy()                                   # the reference's INTT works in place on its input when it can
+        t0 = time.perf_counter()
+        self._extend_pol(_ptr(out), _ptr(src), n_ext, n, ncols, _ptr(buf), 3, 1)
+        t_lde = time.perf_counter() - t0
+        del buf, src
+        tree = np.zeros(self._tree_num_elements(leaf_rows), dtype=np.uint64)
+        t0 = time.perf_counter()
+        self._merkletree(_ptr(tree), _ptr(out), ncols, leaf_rows, 0, 1)
+        t_tree = time.perf_counter() - t0
+        four = np.ascontiguousarray(out[:leaf_rows, :4]) if ncols >= 4 else np.zeros((leaf_rows, 4), dtype=np.uint64)
+        t0 = time.perf_counter()
+        self._merkletree(_ptr(tree), _ptr(four), 4, leaf_rows, 0, 1)
+        t_levels = time.perf_counter() - t0
+        return t_lde, t_tree, t_levels
+
+
 class RefLib(_Lib):
     """The compiled reference, plus the entry points only it has (MerkleTreeGL, root, ...)."""
 

@@ -350,3 +350,59 @@ def check_deferred_rows(ctx, oracle, rng, nrows=4096, device=False):
     before = ctx.leaf_redo_rows()
     check_equal(run_merkletree(ctx, b, device=device), oracle.merkletree(b), "merkletree whose level-0 nodes take the exact path")
     assert ctx.leaf_redo_rows() - before >= made
+
+
+def check_multi(make_multi, oracle, rng, worlds=(2, 4), shapes=((64, 2, 40), (32, 4, 21), (128, 2, 660 // 8), (16, 2, 9), (8, 2, 3))):
+    """glp_multi_* (several devices, one process; csrc/multi.cuh): extendPol, merkletree and the fused commit must give the
+    single-device / oracle bits for every device count, including shapes too small to split (they run on one device)."""
+    for G in worlds:
+        m = make_multi(G)
+        try:
+            assert m.device_count() == G
+            for n, blow, ncols in shapes:
+                n_ext = n * blow
+                a = edge_matrix(rng, n, ncols)
+                want_ext = oracle.extend_pol(a, n_ext)
+                want_tree = oracle.merkletree(want_ext)
+                ext = np.zeros((n_ext, ncols), dtype=np.uint64)
+                m.extend_pol(ext, a, n_ext, n, ncols)
+                check_equal(ext, want_ext, "multi extend_pol G=%d %dx%d" % (G, n, ncols))
+                tree = np.zeros(tree_words(n_ext), dtype=np.uint64)
+                m.merkletree(tree, ext, ncols, n_ext)
+                check_equal(tree, want_tree, "multi merkletree G=%d %dx%d" % (G, n_ext, ncols))
+                ext2 = np.zeros((n_ext, ncols), dtype=np.uint64)
+                tree2 = np.zeros(tree_words(n_ext), dtype=np.uint64)
+                root = m.commit(ext2, tree2, a, n, n_ext, ncols)
+                check_equal(ext2, want_ext, "multi commit ext G=%d %dx%d" % (G, n, ncols))
+                check_equal(tree2, want_tree, "multi commit tree G=%d %dx%d" % (G, n, ncols))
+                check_equal(root, want_tree[-4:], "multi commit root G=%d" % G)
+                root_only = m.commit(None, None, a, n, n_ext, ncols)
+                check_equal(root_only, want_tree[-4:], "multi commit, root only, G=%d" % G)
+        finally:
+            m.close()
+
+
+def check_group_proofs(ctx, reference, rng, device=True, shapes=((256, 21), (1 << 12, 3), (64, 128), (2, 5), (1, 9))):
+    """glp_merkle_group_proofs (all the proofs a tree owes the FRI query phase in one launch / one download) against the
+    reference's own MerkleTreeGL::getGroupProof called once per index (merkleTreeGL.cpp:12-35, friProve.cpp:219-250)"""
+    for h, w in shapes:
+        src = edge_matrix(rng, h, w)
+        nodes, root, psize, group_proof = reference.merkle_tree_gl(src)
+        canon = reference.canonical(src)
+        idx = np.array([0, h - 1, h // 2] + [int(x) for x in rng.integers(0, h, size=29)], dtype=np.uint64)
+        want = np.stack([group_proof(int(i)) for i in idx])
+        words = w + 4 * psize
+        got = np.zeros((idx.size, words), dtype=np.uint64)
+        ctx.merkle_group_proofs(got, src, nodes, w, h, idx)                     # host-resident tree: gathered where it is
+        check_equal(got, want, "group proofs, host tree %dx%d" % (h, w))
+        if device:
+            dsrc, dnodes = ctx.to_device(src), ctx.to_device(nodes)
+            got2 = np.zeros((idx.size, words), dtype=np.uint64)
+            ctx.merkle_group_proofs(got2, dsrc, dnodes, w, h, idx)              # device-resident tree: one launch, one download
+            check_equal(got2, want, "group proofs, device tree %dx%d" % (h, w))
+            one = np.zeros(words, dtype=np.uint64)
+            ctx.merkle_group_proof(one, dsrc, dnodes, w, h, int(idx[3]))
+            check_equal(one, want[3], "single proof")
+            ctx.device_free(dsrc)
+            ctx.device_free(dnodes)
+        del canon

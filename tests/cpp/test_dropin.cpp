@@ -181,6 +181,40 @@ static void test_transcript()
         EXPECT_EQ(perm[i], want[i]);
 }
 
+// Starks::genProof step 1 as starks.cpp:53-57 writes it -- extendPol, then merkelize() -- on a matrix wide and tall enough to be
+// split over the devices of GLP_DEVICES; prints the root and checksums so that the caller (tests/test_cpp_dropin.py) can compare
+// runs with different device lists: the bits must not depend on the device count.
+static void test_commit_sequence()
+{
+    const uint64_t N = 1 << 12, NE = 1 << 13, C = 40;
+    std::vector<El> a = fib_matrix(N, C, N), ext(NE * C);
+    NTT_Goldilocks ntt(N);
+    ntt.extendPol(ext.data(), a.data(), NE, N, C);
+    MerkleTreeGL mt(NE, C, ext.data());
+    mt.merkelize();
+    El root[4];
+    mt.getRoot(root);
+    uint64_t ck_ext = 0, ck_nodes = 0;
+    for (uint64_t i = 0; i < NE * C; i++)
+        ck_ext = ck_ext * 0x9E3779B97F4A7C15ULL + Goldilocks::toU64(ext[i]);
+    for (uint64_t i = 0; i < mt.getTreeNumElements(); i++)
+        ck_nodes = ck_nodes * 0x9E3779B97F4A7C15ULL + Goldilocks::toU64(mt.nodes[i]);
+    printf("commit root %016llx %016llx %016llx %016llx ext %016llx nodes %016llx devices %zu\n", (unsigned long long)Goldilocks::toU64(root[0]),
+           (unsigned long long)Goldilocks::toU64(root[1]), (unsigned long long)Goldilocks::toU64(root[2]), (unsigned long long)Goldilocks::toU64(root[3]),
+           (unsigned long long)ck_ext, (unsigned long long)ck_nodes, glp::device_list().size());
+    // an NTT through an object built with extension > 1 reads the upper rows as zero (ntt_goldilocks.cpp:259-277)
+    const uint64_t M = 64, K = 3;
+    std::vector<El> x = fib_matrix(M, K, M), z = x, y1(M * K), y2(M * K);
+    for (uint64_t i = M / 2; i < M; i++)
+        for (uint64_t j = 0; j < K; j++)
+            z[i * K + j].fe = 0;
+    NTT_Goldilocks ext2(M, 0, 2), plain(M);
+    ext2.NTT(y1.data(), x.data(), M, K);
+    plain.NTT(y2.data(), z.data(), M, K);
+    for (uint64_t i = 0; i < M * K; i++)
+        EXPECT_EQ(Goldilocks::toU64(y1[i]), Goldilocks::toU64(y2[i]));
+}
+
 int main()
 {
     test_errors_and_inert();
@@ -188,6 +222,7 @@ int main()
     test_ntt_roundtrip();
     test_merkletree();
     test_transcript();
+    test_commit_sequence();
     if (failures)
     {
         printf("%d failure(s)\n", failures);

@@ -43,8 +43,33 @@ def test_dropin_headers_next_to_reference_field_header(tmp_path):
     assert r.returncode == 0, r.stderr
 
 
+def _run(exe, **env):
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300, env=dict(os.environ, **env))
+    assert r.returncode == 0 and "dropin ok" in r.stdout, r.stdout + r.stderr
+    line = [l for l in r.stdout.splitlines() if l.startswith("commit root")][0]
+    return line.split(" devices ")[0], int(line.split(" devices ")[1])
+
+
 @pytest.mark.gpu
 def test_dropin_known_answers_on_gpu(ctx):
     exe = build_binary()
-    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and "dropin ok" in r.stdout, r.stdout + r.stderr
+    _run(exe)
+
+
+@pytest.mark.gpu
+def test_dropin_same_bits_for_every_device_list(ctx):
+    """GLP_DEVICES: extendPol + merkelize() through the unchanged call sequence on 1, 2 and 4 contexts -- the same device
+    listed several times on a one-GPU box, distinct devices (peer access over NVLink) when the box has them."""
+    import torch
+    exe = build_binary()
+    base, nd = _run(exe, GLP_DEVICES="0")
+    assert nd == 1
+    lists = ["0,0", "0,0,0,0"]
+    ndev = torch.cuda.device_count()
+    if ndev >= 2:
+        lists.append("0,1")
+    if ndev >= 4:
+        lists.append("0,1,2,3")
+    for devs in lists:
+        got, nd = _run(exe, GLP_DEVICES=devs)
+        assert nd == len(devs.split(",")) and got == base, (devs, got, base)

@@ -568,3 +568,140 @@ def test_overlapped_commit_knob(oracle, rng):
         check_commit(c, oracle, edge_matrix(rng, 1 << 14, 200), 1 << 15, device=True)
     finally:
         c.close()
+
+
+# ---------------------------------------------------------------- full-size known answers and the headline shape
+def test_reference_bench_merkle_root_2p23_x_128(ctx, golden):
+    """The reference's own large known answer: MERKLETREE_BENCH hashes the 2^23 x 128 column-Fibonacci matrix and asserts the
+    root (src/goldilocks/benchs/bench.cpp:406-443).  The matrix (8.6 GB) is generated on the device."""
+    import torch
+    nrows, ncols = 1 << 23, 128
+    dev = torch.device("cuda", 0)
+    a = torch.empty(nrows * ncols, dtype=torch.int64, device=dev)
+    ctx.fib_fill(a, nrows, ncols)
+    # the generator itself: its first rows and a strip in the middle against the host recurrence
+    head = a[: 64 * ncols].cpu().numpy().view(np.uint64).reshape(64, ncols)
+    check_equal(head, fib_matrix(64, ncols), "device Fibonacci matrix, first rows")
+    j = 5 * 512 - 2                                              # straddles a chunk boundary of the generator
+    strip = a[j * ncols: (j + 4) * ncols].cpu().numpy().view(np.uint64).reshape(4, ncols)
+    assert all((int(strip[2, c]) == (int(strip[0, c]) + int(strip[1, c])) % P) and (int(strip[3, c]) == (int(strip[1, c]) + int(strip[2, c])) % P)
+               for c in range(ncols))
+    tree = torch.empty(tree_words(nrows), dtype=torch.int64, device=dev)
+    ctx.merkletree(tree, a, ncols, nrows)
+    root = tree[-4:].cpu().numpy().view(np.uint64)
+    check_equal(root, golden["bench_merkletree_8388608x128_root"]["out"], "bench.cpp MERKLETREE_BENCH root")
+
+
+def test_config_b_full_size(ctx, oracle):
+    """BASELINE.json configs[1] at its real size, 2^23 x 660 -> 2^24 (134 GB resident): whole columns of the extension -- the
+    first, the last, and both sides of 32-lane group and 8-column sponge-block edges -- against the oracle's extendPol of the
+    same columns, 48 Merkle paths (row -> leaf hash -> every sibling -> root) recomputed with the oracle's hashes, and the root
+    against the committed value bench.py compares every N with."""
+    import torch
+    from xlayer_prover_b200 import synth_matrix
+    free, _ = torch.cuda.mem_get_info(0)
+    n, n_ext, C = 1 << 23, 1 << 24, 660
+    need = 8 * (n * C + n_ext * C) + 8 * tree_words(n_ext) + (14 << 30)
+    if free < need:
+        pytest.skip("needs %.0f GB of device memory, %.0f GB free" % (need / 1e9, free / 1e9))
+    seed = 0x9E3779B97F4A7C15 + 2
+    dev = torch.device("cuda", 0)
+    din = torch.empty(n * C, dtype=torch.int64, device=dev)
+    ctx.synth_fill(din, n, C, seed)
+    dext = torch.empty(n_ext * C, dtype=torch.int64, device=dev)
+    dtree = torch.empty(tree_words(n_ext), dtype=torch.int64, device=dev)
+    retries0 = ctx.ntt_retry_count()
+    root = ctx.commit(dext, dtree, din, n, n_ext, C)
+    assert ctx.ntt_retry_count() == retries0, "uniform synthetic data must not trip the optimistic LDE"
+    del din
+    ext = dext.view(n_ext, C)
+    cols = [0, 7, 8, 31, 32, 63, 64, 329, 639, 640, 655, 656, 659]
+    a = np.concatenate([synth_matrix(n, 1, seed, col0=c, ncols_total=C) for c in cols], axis=1)
+    want = oracle.extend_pol(a, n_ext)
+    got = ext[:, cols].cpu().numpy().view(np.uint64)
+    check_equal(got, want, "whole columns %s of the 2^24 x 660 extension" % cols)
+    tree = dtree.cpu().numpy().view(np.uint64)
+    depth = 24
+    prng = np.random.default_rng(7)
+    for idx in [0, 1, n_ext - 1, n_ext // 2 - 1, n_ext // 2] + [int(x) for x in prng.integers(0, n_ext, size=43)]:
+        row = ext[idx].cpu().numpy().view(np.uint64)
+        h = oracle.linear_hash(row)
+        check_equal(tree[4 * idx: 4 * idx + 4], h, "leaf %d" % idx)
+        off, nn, i = 0, n_ext, idx
+        for _ in range(depth):
+            sib = tree[off + 4 * (i ^ 1): off + 4 * (i ^ 1) + 4]
+            pair = np.concatenate([h, sib]) if i % 2 == 0 else np.concatenate([sib, h])
+            h = oracle.hash_full_result(np.concatenate([pair, np.zeros(4, dtype=np.uint64)]))[:4]
+            off += 4 * nn
+            nn //= 2
+            i //= 2
+        check_equal(h, tree[-4:], "path of row %d to the root" % idx)
+    check_equal(root, tree[-4:], "root returned by glp_commit")
+    known = np.array([0x2954300a93d8e1ed, 0xb89e6e7f7a6d3906, 0x8e88252716f12068, 0xc8cda114b642004f], dtype=np.uint64)
+    check_equal(root, known, "root of the headline workload (bench.py KNOWN_ROOTS)")
+
+
+def test_group_proofs_batched(ctx, reference, rng):
+    """glp_merkle_group_proofs on device-resident trees, against the reference's MerkleTreeGL::getGroupProof per index"""
+    from cases import check_group_proofs
+    check_group_proofs(ctx, reference, rng, shapes=((256, 21), (1 << 12, 3), (64, 128), (2, 5), (1, 9), (1 << 16, 40)))
+
+
+# ---------------------------------------------------------------- several devices
+def test_multi_contexts_on_one_device(oracle, rng):
+    """glp_multi_* with G = 2 and 4 contexts on device 0 (a host thread each, the slabs in the same memory): the split, the
+    scatter, the subtree placement and the top levels, on real kernels"""
+    from cases import check_multi
+    from xlayer_prover_b200 import MultiContext
+    check_multi(lambda G: MultiContext([0] * G), oracle, rng,
+                shapes=((1 << 12, 2, 72), (1 << 10, 8, 40), (1 << 14, 2, 660 // 4), (64, 2, 21), (8, 2, 3)))
+
+
+def test_multi_commit_two_gpus(ctx, oracle, rng):
+    """glp_multi_commit on two DISTINCT devices: peer stores over NVLink from the LDE's last pass; every extended row and every
+    node against the single-device result of the same library and the oracle"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    from xlayer_prover_b200 import MultiContext, synth_matrix
+    for devs in ([0, 1],) + (([0, 1, 2, 3],) if torch.cuda.device_count() >= 4 else ()):
+        m = MultiContext(devs)
+        try:
+            for n, n_ext, ncols in ((1 << 15, 1 << 16, 72), (1 << 12, 1 << 15, 330), (1 << 16, 1 << 17, 24)):
+                a = synth_matrix(n, ncols, 0xABCDEF)
+                ext1, tree1, root1 = run_commit(ctx, a, n_ext)
+                ext = np.zeros((n_ext, ncols), dtype=np.uint64)
+                tree = np.zeros(tree_words(n_ext), dtype=np.uint64)
+                root = m.commit(ext, tree, a, n, n_ext, ncols)
+                check_equal(ext, ext1, "extension, devices %s" % devs)
+                check_equal(tree, tree1, "nodes, devices %s" % devs)
+                check_equal(root, root1, "root, devices %s" % devs)
+                ext2 = np.zeros((n_ext, ncols), dtype=np.uint64)
+                m.extend_pol(ext2, a, n_ext, n, ncols)
+                check_equal(ext2, ext1, "multi extend_pol, devices %s" % devs)
+                tree2 = np.zeros(tree_words(n_ext), dtype=np.uint64)
+                m.merkletree(tree2, ext2, ncols, n_ext)
+                check_equal(tree2, tree1, "multi merkletree, devices %s" % devs)
+            want = oracle.merkletree(oracle.extend_pol(a, n_ext))
+            check_equal(tree, want, "nodes against the oracle")
+        finally:
+            m.close()
+
+
+def test_sharded_commit_two_gpus(tmp_path):
+    """xlayer_prover_b200/sharded.py on real devices: one process per GPU under torch.distributed.run, NCCL, CUDA IPC and the
+    fused NVLink scatter; every slab row and every node against the N = 1 device result (tests/sharded_gpu_worker.py)"""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    here = os.path.dirname(os.path.abspath(__file__))
+    for world in [2] + ([4] if torch.cuda.device_count() >= 4 else []):
+        out = tmp_path / ("w%d" % world)
+        out.mkdir()
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
+               "--master-port", str(29700 + world), os.path.join(here, "sharded_gpu_worker.py"), str(out), "15", "1", "168"]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+        assert (out / "result.txt").read_text().startswith("slabs_equal=1 tree_equal=1"), (out / "result.txt").read_text()

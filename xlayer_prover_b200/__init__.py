@@ -18,7 +18,7 @@ import math
 
 import numpy as np
 
-from ._capi import (Context, GlpError, GlpLib, P, load, ptr_of, splitmix, synth_matrix, tree_num_elements,
+from ._capi import (Context, GlpError, GlpLib, MultiContext, P, load, ptr_of, splitmix, synth_matrix, tree_num_elements,
                     GLP_E_ARG, GLP_E_DOMAIN, GLP_E_CUDA, GLP_E_OOM)
 
 RATE, CAPACITY, HASH_SIZE, SPONGE_WIDTH = 8, 4, 4, 12

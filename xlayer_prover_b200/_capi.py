@@ -38,6 +38,7 @@ SIGNATURES = {
     "glp_memcpy": (i32, [vp, vp, vp, u64]),
     "glp_mem_info": (i32, [vp, u64p, u64p]),
     "glp_ntt": (i32, [vp, vp, vp, u64, u64, i32, i32]),
+    "glp_ntt_live": (i32, [vp, vp, vp, u64, u64, i32, i32, u64]),
     "glp_extend_pol": (i32, [vp, vp, vp, u64, u64, u64]),
     "glp_extend_pol_pitched": (i32, [vp, vp, u64, vp, u64, u64, u64, u64]),
     "glp_extend_pol_scatter": (i32, [vp, C.POINTER(vp), u32, u64, u64, vp, u64, u64, u64, u64]),
@@ -53,6 +54,7 @@ SIGNATURES = {
     "glp_merkletree_batch": (i32, [vp, vp, vp, u64, u64, u64, u64]),
     "glp_merkle_levels": (i32, [vp, vp, u64]),
     "glp_tree_num_elements": (u64, [u64]),
+    "glp_merkle_group_proofs": (i32, [vp, vp, vp, vp, u64, u64, vp, u64]),
     "glp_merkle_group_proof": (i32, [vp, vp, vp, vp, u64, u64, u64]),
     "glp_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64]),
     "glp_quotient_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64, u64]),
@@ -61,11 +63,20 @@ SIGNATURES = {
     "glp_fri_fold": (i32, [vp, vp, vp, u32, u32, vp, u64]),
     "glp_fri_group_tree": (i32, [vp, vp, vp, vp, vp, u32, u32]),
     "glp_synth_fill": (i32, [vp, vp, u64, u64, u64, u64, u64, u64]),
+    "glp_fib_fill": (i32, [vp, vp, u64, u64]),
     "glp_checksum": (i32, [vp, vp, u64, u64p]),
     "glp_field_selftest": (i32, [vp, vp, vp, u64, vp]),
     "glp_set_profiling": (i32, [vp, i32]),
     "glp_get_profile": (i32, [vp, C.POINTER(C.c_float), C.POINTER(u32)]),
     "glp_measure_int_peak": (i32, [vp, C.POINTER(C.c_double)]),
+    "glp_measure_pipe_peaks": (i32, [vp, C.POINTER(C.c_double)]),
+    "glp_multi_init": (i32, [i32, C.POINTER(i32), C.POINTER(vp)]),
+    "glp_multi_destroy": (None, [vp]),
+    "glp_multi_device_count": (i32, [vp]),
+    "glp_multi_ctx": (vp, [vp, i32]),
+    "glp_multi_extend_pol": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_multi_merkletree": (i32, [vp, vp, vp, u64, u64, u64]),
+    "glp_multi_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64]),
 }
 
 
@@ -192,8 +203,16 @@ class Context:
         return out
 
     # ---- the path
-    def ntt(self, dst, src, size, ncols=1, inverse=False, extend=False):
-        self.lib.check(self.lib.glp_ntt(self.h, ptr_of(dst), ptr_of(src), size, ncols, int(inverse), int(extend)))
+    def ntt(self, dst, src, size, ncols=1, inverse=False, extend=False, live_rows=None):
+        """live_rows: rows >= live_rows of src are read as zero (an NTT_Goldilocks object built with extension > 1)"""
+        if live_rows is None:
+            self.lib.check(self.lib.glp_ntt(self.h, ptr_of(dst), ptr_of(src), size, ncols, int(inverse), int(extend)))
+        else:
+            self.lib.check(self.lib.glp_ntt_live(self.h, ptr_of(dst), ptr_of(src), size, ncols, int(inverse), int(extend), live_rows))
+
+    def fib_fill(self, dst, nrows, ncols):
+        """the reference's Fibonacci test matrix (bench.cpp:410-427), generated on the device"""
+        self.lib.check(self.lib.glp_fib_fill(self.h, ptr_of(dst), nrows, ncols))
 
     def extend_pol(self, out, inp, n_ext, n, ncols):
         self.lib.check(self.lib.glp_extend_pol(self.h, ptr_of(out), ptr_of(inp), n_ext, n, ncols))
@@ -241,6 +260,11 @@ class Context:
 
     def merkle_group_proof(self, proof, source, nodes, width, height, idx):
         self.lib.check(self.lib.glp_merkle_group_proof(self.h, ptr_of(proof), ptr_of(source), ptr_of(nodes), width, height, idx))
+
+    def merkle_group_proofs(self, proofs, source, nodes, width, height, idx):
+        """getGroupProof for every index of `idx` (a host uint64 array) in one launch / one download"""
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        self.lib.check(self.lib.glp_merkle_group_proofs(self.h, ptr_of(proofs), ptr_of(source), ptr_of(nodes), width, height, ptr_of(idx), idx.size))
 
     def commit(self, out_ext, tree, inp, n, n_ext, ncols):
         root = np.zeros(4, dtype=np.uint64)
@@ -298,6 +322,49 @@ class Context:
         out = (C.c_double * 3)()
         self.lib.check(self.lib.glp_measure_int_peak(self.h, out))
         return {"imad_lane_ops_per_s": out[0], "iadd3_lane_ops_per_s": out[1], "interleaved_lane_ops_per_s": out[2]}
+
+    def measure_pipe_peaks(self):
+        """lane-ops/s of IMAD, IADD3, both interleaved, IMAD.WIDE (64-bit accumulate) and DFMA on this device"""
+        out = (C.c_double * 5)()
+        self.lib.check(self.lib.glp_measure_pipe_peaks(self.h, out))
+        return {"imad_lane_ops_per_s": out[0], "iadd3_lane_ops_per_s": out[1], "interleaved_lane_ops_per_s": out[2],
+                "imad_wide_lane_ops_per_s": out[3], "dfma_lane_ops_per_s": out[4]}
+
+
+class MultiContext:
+    """One glp_multi: G devices driven from this process (include/glprover.h, csrc/multi.cuh).  Host buffers only."""
+
+    def __init__(self, devices, lib=None):
+        self.lib = lib or load()
+        devs = (i32 * len(devices))(*devices)
+        h = vp()
+        self.lib.check(self.lib.glp_multi_init(len(devices), devs, C.byref(h)))
+        self.h = h
+        self.devices = list(devices)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.glp_multi_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def device_count(self): return int(self.lib.glp_multi_device_count(self.h))
+
+    def extend_pol(self, out, inp, n_ext, n, ncols):
+        self.lib.check(self.lib.glp_multi_extend_pol(self.h, ptr_of(out), ptr_of(inp), n_ext, n, ncols))
+
+    def merkletree(self, tree, inp, ncols, nrows, dim=1):
+        self.lib.check(self.lib.glp_multi_merkletree(self.h, ptr_of(tree), ptr_of(inp), ncols, nrows, dim))
+
+    def commit(self, out_ext, tree, inp, n, n_ext, ncols):
+        root = np.zeros(4, dtype=np.uint64)
+        self.lib.check(self.lib.glp_multi_commit(self.h, ptr_of(out_ext), ptr_of(tree), ptr_of(root), ptr_of(inp), n, n_ext, ncols))
+        return root
 
 
 def tree_num_elements(nrows):

@@ -67,6 +67,27 @@ __global__ void k_group_proof(gl_t *proof, const gl_t *source, const gl_t *nodes
     }
 }
 
+// The same for a batch of query indices (the FRI query phase asks every tree for every query index,
+// src/starkpil/fri/friProve.cpp:150-170,219-250): CTA q gathers proof q = [row idx[q] | siblings] into proofs + q * stride.
+__global__ void k_group_proofs(gl_t *proofs, uint64_t stride, const gl_t *source, const gl_t *nodes, uint64_t width, uint64_t height,
+                               const uint64_t *idx, uint64_t nidx)
+{
+    const uint64_t q = blockIdx.x;
+    if (q >= nidx) return;
+    const uint64_t row = idx[q];
+    gl_t *proof = proofs + q * stride;
+    for (uint64_t i = threadIdx.x; i < width; i += blockDim.x) proof[i] = gl_canon(source[row * width + i]);
+    // one thread per (level, word): the path is at most 32 levels x 4 words
+    uint64_t depth = 0;
+    while (((uint64_t)1 << depth) < height) depth++;
+    for (uint64_t t = threadIdx.x; t < 4 * depth; t += blockDim.x) {
+        const uint64_t lvl = t >> 2, w = t & 3;
+        // offset of level lvl = 4 * (height + height/2 + ... ) = 4 * (2*height - (2*height >> lvl))
+        const uint64_t offset = 4 * (2 * height - ((2 * height) >> lvl));
+        proof[width + t] = nodes[offset + ((row >> lvl) ^ 1) * 4 + w];
+    }
+}
+
 // Step 4 of Starks::genProof (src/starkpil/starks.cpp:264-281): the quotient's coefficients qq1 [qdeg*n x qdim] are cut
 // into qdeg chunks of n and chunk p, scaled by shift_in^p (shift_in = shift^-n), becomes columns [p*qdim, (p+1)*qdim) of
 // the n-row matrix qq2:  qq2[k][p*qdim + d] = qq1[p*n + k][d] * shift_in^p.
@@ -109,64 +130,87 @@ __global__ void k_field_selftest(const gl_t *a, const gl_t *b, uint64_t n, gl_t 
     out[GLP_SELFTEST_OUTS * i + 7] = gl_canon(gl_add_c(x, gl_canon(y)));
 }
 
+// ---- the reference's Fibonacci test matrix, generated on the device ----
+// dst[j*ncols + i] = (i + 1) * F_j mod p with F_0 = F_1 = 1, F_j = F_(j-2) + F_(j-1): the input of the reference's Merkle
+// benchmark and tests (src/goldilocks/benchs/bench.cpp:410-427, tests/tests.cpp:1822-1835), whose 2^23 x 128 root is a known
+// answer (bench.cpp:440-443).  One thread owns one column of one chunk of rows: it jumps to the chunk's first row with the
+// fast-doubling identities fib(2k) = fib(k) (2 fib(k+1) - fib(k)), fib(2k+1) = fib(k)^2 + fib(k+1)^2 and then walks the recurrence.
+#define GLP_FIB_CHUNK 512
+__global__ void k_fib_fill(gl_t *dst, uint64_t nrows, uint64_t ncols)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nchunks = (nrows + GLP_FIB_CHUNK - 1) / GLP_FIB_CHUNK;
+    if (t >= nchunks * ncols) return;
+    const uint64_t col = t % ncols, j0 = (t / ncols) * GLP_FIB_CHUNK;
+    // (a, b) = (fib(m), fib(m+1)) for m = j0 + 1  (standard fib(0) = 0, fib(1) = 1; F_j = fib(j + 1))
+    const uint64_t m = j0 + 1;
+    gl_t a = 0, b = 1;
+    for (int bit = 63; bit >= 0; bit--) {
+        const gl_t c = gl_mul(a, gl_sub(gl_add(b, b), a));         // fib(2k)
+        const gl_t d = gl_add(gl_mul(a, a), gl_mul(b, b));         // fib(2k+1)
+        a = c;
+        b = d;
+        if ((m >> bit) & 1) { const gl_t e = gl_add(a, b); a = b; b = e; }
+    }
+    const gl_t k = col + 1;
+    gl_t v0 = gl_mul(a, k), v1 = gl_mul(b, k);
+    const uint64_t j1 = j0 + GLP_FIB_CHUNK < nrows ? j0 + GLP_FIB_CHUNK : nrows;
+    for (uint64_t j = j0; j < j1; j++) {
+        dst[j * ncols + col] = gl_canon(v0);
+        const gl_t nx = gl_add(v0, v1);
+        v0 = v1;
+        v1 = nx;
+    }
+}
+
 // ---- integer-pipe peak micro-benchmarks ("the IMAD peak must be measured on the box") ----
-// mode 0: 8 independent IMAD (32-bit multiply-add, same pipe as IMAD.WIDE) chains per thread; mode 1: 8 independent IADD3 chains; mode 2: both interleaved.
-// Each loop iteration issues 8 (mode 0/1) or 16 (mode 2) dependent-free integer instructions per thread.
-__global__ void k_int_peak(uint64_t *sink, uint32_t iters, int mode)
+// MODE 0: 8 independent IMAD (32-bit multiply-add, same pipe as IMAD.WIDE) chains per thread; 1: 8 independent IADD3 chains; 2: both
+// interleaved; 3: 8 independent IMAD.WIDE chains (32x32 -> 64 with a 64-bit accumulate, written as the mad.lo.cc / madc.hi pair
+// ptxas keeps as ONE instruction); 4: 8 independent DFMA chains.  3 and 4 are the two instruction classes the algorithmic floor
+// of the Poseidon permutation is counted in (bench.py roofline).  Each loop iteration issues 8 (16 in mode 2) dependent-free
+// instructions per thread.  MODE is a template parameter: with a run-time mode every flavour shared one register allocation and
+// one schedule, and adding a mode changed the numbers of the others.
+template <int MODE>
+__global__ void k_int_peak(uint64_t *sink, uint32_t iters)
 {
     uint32_t a = threadIdx.x * 2654435761u + 12345u, b = (blockIdx.x * 40503u + 977u) ^ (threadIdx.x * 97u);
     uint32_t m0 = a, m1 = b, m2 = a ^ b, m3 = a + b, m4 = a * 3u, m5 = b * 5u, m6 = a * 7u, m7 = b * 11u;
     uint32_t s0 = a, s1 = b, s2 = a ^ 1u, s3 = b ^ 2u, s4 = a ^ 3u, s5 = b ^ 4u, s6 = a ^ 5u, s7 = b ^ 6u;
+    double d0 = (double)a, d1 = (double)b, d2 = d0 + 1.0, d3 = d1 + 2.0, d4 = d0 + 3.0, d5 = d1 + 4.0, d6 = d0 + 5.0, d7 = d1 + 6.0;
+    const double dm = 1.0000000001, dc = 3.0;
     // every operand is loop-carried, so ptxas can neither hoist the product nor fold the adds
 #if GL_DEVICE_PTX
 #define GLP_MADW(acc, y) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(acc) : "r"(y), "r"(a))
 #define GLP_ADD3(acc, x, y) asm volatile("{ .reg .u32 t; add.u32 t, %1, %2; add.u32 %0, %0, t; }" : "+r"(acc) : "r"(x), "r"(y))
-#else
-#define GLP_MADW(acc, y) acc = acc * (y) + a
-#define GLP_ADD3(acc, x, y) acc += (x) + (y)
-#endif
-    if (mode >= 3) {
-        // mode 3: 8 independent IMAD.WIDE chains (32x32 -> 64 with a 64-bit accumulate, written as the mad.lo.cc / madc.hi pair
-        // ptxas keeps as ONE instruction); mode 4: 8 independent DFMA chains.  The two instruction classes the algorithmic
-        // floor of the Poseidon permutation is made of (bench.py roofline).
-        double d0 = (double)a, d1 = (double)b, d2 = d0 + 1.0, d3 = d1 + 2.0, d4 = d0 + 3.0, d5 = d1 + 4.0, d6 = d0 + 5.0, d7 = d1 + 6.0;
-        const double dm = 1.0000000001, dc = 3.0;
-#if GL_DEVICE_PTX
 #define GLP_MADWIDE(lo, hi, y) asm volatile("{ mad.lo.cc.u32 %0, %2, %3, %0; madc.hi.u32 %1, %2, %3, %1; }" : "+r"(lo), "+r"(hi) : "r"(y), "r"(a))
 #define GLP_DFMA(acc) asm volatile("fma.rn.f64 %0, %0, %1, %2;" : "+d"(acc) : "d"(dm), "d"(dc))
 #else
+#define GLP_MADW(acc, y) acc = acc * (y) + a
+#define GLP_ADD3(acc, x, y) acc += (x) + (y)
 #define GLP_MADWIDE(lo, hi, y) { uint64_t t_ = (((uint64_t)(hi) << 32) | (lo)) + (uint64_t)(y) * a; lo = (uint32_t)t_; hi = (uint32_t)(t_ >> 32); }
 #define GLP_DFMA(acc) acc = acc * dm + dc
 #endif
-        for (uint32_t i = 0; i < iters; i++) {
-#pragma unroll
-            for (int r = 0; r < 8; r++) {
-                if (mode == 3) {
-                    GLP_MADWIDE(m0, s0, b); GLP_MADWIDE(m1, s1, b); GLP_MADWIDE(m2, s2, b); GLP_MADWIDE(m3, s3, b);
-                    GLP_MADWIDE(m4, s4, b); GLP_MADWIDE(m5, s5, b); GLP_MADWIDE(m6, s6, b); GLP_MADWIDE(m7, s7, b);
-                } else {
-                    GLP_DFMA(d0); GLP_DFMA(d1); GLP_DFMA(d2); GLP_DFMA(d3); GLP_DFMA(d4); GLP_DFMA(d5); GLP_DFMA(d6); GLP_DFMA(d7);
-                }
-            }
-        }
-        const double ds = d0 + d1 + d2 + d3 + d4 + d5 + d6 + d7;
-        const uint32_t rr = m0 ^ m1 ^ m2 ^ m3 ^ m4 ^ m5 ^ m6 ^ m7 ^ s0 ^ s1 ^ s2 ^ s3 ^ s4 ^ s5 ^ s6 ^ s7;
-        if (rr == iters * 0x9E3779B1u + 7u || ds == 0.125) sink[0] = rr;
-        return;
-    }
     for (uint32_t i = 0; i < iters; i++) {
 #pragma unroll
         for (int r = 0; r < 8; r++) {
-            if (mode != 1) {
+            if (MODE == 0 || MODE == 2) {
                 GLP_MADW(m0, b); GLP_MADW(m1, b); GLP_MADW(m2, b); GLP_MADW(m3, b);
                 GLP_MADW(m4, b); GLP_MADW(m5, b); GLP_MADW(m6, b); GLP_MADW(m7, b);
             }
-            if (mode != 0) {
+            if (MODE == 1 || MODE == 2) {
                 GLP_ADD3(s0, s4, s5); GLP_ADD3(s1, s5, s6); GLP_ADD3(s2, s6, s7); GLP_ADD3(s3, s7, s4);
                 GLP_ADD3(s4, s0, s1); GLP_ADD3(s5, s1, s2); GLP_ADD3(s6, s2, s3); GLP_ADD3(s7, s3, s0);
             }
+            if (MODE == 3) {
+                GLP_MADWIDE(m0, s0, b); GLP_MADWIDE(m1, s1, b); GLP_MADWIDE(m2, s2, b); GLP_MADWIDE(m3, s3, b);
+                GLP_MADWIDE(m4, s4, b); GLP_MADWIDE(m5, s5, b); GLP_MADWIDE(m6, s6, b); GLP_MADWIDE(m7, s7, b);
+            }
+            if (MODE == 4) {
+                GLP_DFMA(d0); GLP_DFMA(d1); GLP_DFMA(d2); GLP_DFMA(d3); GLP_DFMA(d4); GLP_DFMA(d5); GLP_DFMA(d6); GLP_DFMA(d7);
+            }
         }
     }
-    uint32_t r = m0 ^ m1 ^ m2 ^ m3 ^ m4 ^ m5 ^ m6 ^ m7 ^ s0 ^ s1 ^ s2 ^ s3 ^ s4 ^ s5 ^ s6 ^ s7;
-    if (r == iters * 0x9E3779B1u + 7u) sink[0] = r;   // practically never true; keeps the chains alive
+    const double ds = d0 + d1 + d2 + d3 + d4 + d5 + d6 + d7;
+    const uint32_t r = m0 ^ m1 ^ m2 ^ m3 ^ m4 ^ m5 ^ m6 ^ m7 ^ s0 ^ s1 ^ s2 ^ s3 ^ s4 ^ s5 ^ s6 ^ s7;
+    if (r == iters * 0x9E3779B1u + 7u || (MODE == 4 && ds == 0.125)) sink[0] = r;   // practically never true; keeps the chains alive
 }

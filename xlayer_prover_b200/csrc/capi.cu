@@ -715,8 +715,9 @@ static uint32_t pick_block_cols(glp_ctx *ctx, uint64_t rows_total, uint64_t ncol
 
 // device pointers only
 static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src, uint64_t src_pitch, uint64_t size, uint64_t ncols,
-                   bool inverse, bool extend)
+                   bool inverse, bool extend, uint64_t live = 0)
 {
+    if (!live || live > size) live = size;
     const uint32_t logN = ilog2_u64(size);
     NttPlanLogs pl;
     if (!plan_passes(ctx, logN, &pl)) return fail(GLP_E_ARG, "NTT: size exceeds four tile passes");
@@ -727,7 +728,7 @@ static int dev_ntt(glp_ctx *ctx, gl_t *dst, uint64_t dst_pitch, const gl_t *src,
     }
     for (uint64_t c0 = 0; c0 < ncols; c0 += wb) {
         const uint32_t w = (uint32_t)((ncols - c0 < wb) ? ncols - c0 : wb);
-        GLP(run_transform(ctx, logN, src + c0, src_pitch, dst + c0, dst_pitch, w, size, inverse, extend, (gl_t *)ctx->s1.p));
+        GLP(run_transform(ctx, logN, src + c0, src_pitch, dst + c0, dst_pitch, w, live, inverse, extend, (gl_t *)ctx->s1.p));
     }
     return GLP_OK;
 }
@@ -832,6 +833,11 @@ static int stage_in(glp_ctx *ctx, DevBuf &buf, const uint64_t *p, size_t words, 
 // ------------------------------------------------------------------------------------------------
 extern "C" int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend)
 {
+    return glp_ntt_live(ctx, dst, src, size, ncols, inverse, extend, size);
+}
+extern "C" int glp_ntt_live(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size, uint64_t ncols, int inverse, int extend,
+                            uint64_t live_rows)
+{
     if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
     if (size == 0 || ncols == 0) return GLP_OK;                 // ntt_goldilocks.cpp:168-171
     if (!src) return fail(GLP_E_ARG, "glp_ntt: src is NULL");
@@ -850,7 +856,11 @@ extern "C" int glp_ntt(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_
         if ((const void *)dsrc == ctx->tmp_in.p) ddst = (gl_t *)ctx->tmp_in.p;
         else { GLP(ensure(ctx, ctx->tmp_out, words * sizeof(gl_t))); ddst = (gl_t *)ctx->tmp_out.p; }
     }
-    GLP(dev_ntt(ctx, ddst, ncols, dsrc, ncols, size, ncols, inverse != 0, inverse != 0 && extend != 0));
+    if (live_rows == 0) {                                        // everything is read as zero: the transform of zero
+        CU(cudaMemsetAsync(ddst, 0, words * sizeof(gl_t), ctx->stream));
+    } else {
+        GLP(dev_ntt(ctx, ddst, ncols, dsrc, ncols, size, ncols, inverse != 0, inverse != 0 && extend != 0, live_rows));
+    }
     if (!dst_dev) CU(cudaMemcpyAsync(dst, ddst, words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return GLP_OK;
@@ -1272,6 +1282,54 @@ extern "C" int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint6
     return GLP_OK;
 }
 
+// All the proofs one tree owes to the FRI query phase in ONE launch and ONE download (friProve.cpp:150-170 asks each of the
+// five trees for every query index through queryPol, :219-250): proofs[q * (width + 4*depth) ...] = getGroupProof(idx[q]).
+// With source and nodes resident on the device this is what makes "keep cm1..cm4 on the device, download only roots,
+// query rows and paths" usable: nidx * (width + 4*depth) words cross the link instead of the whole extension.
+extern "C" int glp_merkle_group_proofs(glp_ctx *ctx, uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width,
+                                       uint64_t height, const uint64_t *idx, uint64_t nidx)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (nidx == 0) return GLP_OK;
+    if (!proofs || !nodes || !idx || (!source && width)) return fail(GLP_E_ARG, "glp_merkle_group_proofs: NULL pointer");
+    if (!is_pow2(height)) return fail(GLP_E_ARG, "glp_merkle_group_proofs: height must be a power of two");
+    if (on_device(idx)) return fail(GLP_E_ARG, "glp_merkle_group_proofs: idx is a host array");
+    for (uint64_t q = 0; q < nidx; q++)
+        if (idx[q] >= height) return fail(GLP_E_ARG, "glp_merkle_group_proofs: index out of range");
+    const uint64_t depth = ilog2_u64(height);
+    const uint64_t words = width + 4 * depth;
+    if (!on_device(source) || !on_device(nodes)) {
+        if (on_device(source) || on_device(nodes) || on_device(proofs))
+            return fail(GLP_E_ARG, "glp_merkle_group_proofs: source and nodes must both be host or both be device memory");
+        // host-resident tree: a pure gather, done where the data is (merkleTreeGL.cpp:12-35)
+        for (uint64_t q = 0; q < nidx; q++) {
+            uint64_t *proof = proofs + q * words;
+            for (uint64_t i = 0; i < width; i++) proof[i] = gl_canon(source[idx[q] * width + i]);
+            uint64_t n = height, off = 0, id = idx[q];
+            for (uint64_t l = 0; l < depth; l++) {
+                memcpy(proof + width + 4 * l, nodes + off + (id ^ 1) * 4, 4 * sizeof(uint64_t));
+                off += 4 * n; n >>= 1; id >>= 1;
+            }
+        }
+        return GLP_OK;
+    }
+    CU(cudaSetDevice(ctx->device));
+    if (nidx > 0x7FFFFFFFull) return fail(GLP_E_ARG, "glp_merkle_group_proofs: too many indices");
+    const bool out_dev = on_device(proofs);
+    const size_t out_words = (size_t)nidx * words;
+    // staging: [indices | proofs]
+    GLP(ensure(ctx, ctx->tmp_out, (nidx + (out_dev ? 0 : out_words)) * sizeof(gl_t)));
+    uint64_t *didx = (uint64_t *)ctx->tmp_out.p;
+    gl_t *dproofs = out_dev ? (gl_t *)proofs : (gl_t *)ctx->tmp_out.p + nidx;
+    CU(cudaMemcpyAsync(didx, idx, nidx * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_group_proofs, (unsigned)nidx, 128, 0, dproofs, words, (const gl_t *)source, (const gl_t *)nodes, width, height,
+           (const uint64_t *)didx, nidx);
+    CU(cudaGetLastError());
+    if (!out_dev) CU(cudaMemcpyAsync(proofs, dproofs, out_words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
 // ------------------------------------------------------------------------------------------------
 // fused commit
 // ------------------------------------------------------------------------------------------------
@@ -1285,8 +1343,10 @@ extern "C" int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint6
 // hashes and the level loop runs in place.  out_ext may alias in (same pitch): block k's download only overwrites
 // the columns block k's upload has already read.
 static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64_t *tree, bool tree_dev, gl_t *dtree, uint64_t root[4],
-                           const uint64_t *in, uint64_t n, uint64_t n_ext, uint64_t ncols)
+                           const uint64_t *in, uint64_t n, uint64_t n_ext, uint64_t ncols, uint64_t in_pitch = 0, uint64_t out_pitch = 0)
 {
+    if (!in_pitch) in_pitch = ncols;                              // a column window of a wider host matrix (glp_multi_extend_pol)
+    if (!out_pitch) out_pitch = ncols;
     const bool want_tree = dtree != nullptr;
     const bool want_ext = out_ext != nullptr;
     const size_t tree_words = glp_tree_num_elements(n_ext);
@@ -1349,7 +1409,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     auto width = [&](uint64_t k) { return (uint32_t)(col0[k + 1] - col0[k]); };
     auto upload = [&](uint64_t k) -> int {
         if (k >= 2 && !full_stage) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
-        CU(cudaMemcpy2DAsync(stage_of(k), (size_t)width(k) * 8, in + col0[k], (size_t)ncols * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
+        CU(cudaMemcpy2DAsync(stage_of(k), (size_t)width(k) * 8, in + col0[k], (size_t)in_pitch * 8, (size_t)width(k) * 8, n, cudaMemcpyHostToDevice,
                              ctx->copy_stream[0]));
         CU(cudaEventRecord(up[k], ctx->copy_stream[0]));
         return GLP_OK;
@@ -1362,7 +1422,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         const uint64_t c0 = col0[k];
         const uint32_t wk = width(k);
         gl_t *eb = ext_dev ? (gl_t *)out_ext + c0 : extb[k & 1];
-        const uint64_t eb_pitch = ext_dev ? ncols : wk;
+        const uint64_t eb_pitch = ext_dev ? out_pitch : wk;
         CU(cudaStreamWaitEvent(ctx->stream, up[k], 0));
         if (!ext_dev && want_ext && k >= 2) CU(cudaStreamWaitEvent(ctx->stream, down[k - 2], 0));   // extension buffer still being downloaded
         GLP(lde_block(ctx, logN, logE, stage_of(k), wk, eb, eb_pitch, wk));
@@ -1370,7 +1430,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         if (k + 2 < nblocks && !full_stage) GLP(upload(k + 2));
         if (want_ext && !ext_dev) {
             CU(cudaStreamWaitEvent(ctx->copy_stream[1], lde_done[k], 0));
-            CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)ncols * 8, eb, (size_t)wk * 8, (size_t)wk * 8, n_ext, cudaMemcpyDeviceToHost,
+            CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)out_pitch * 8, eb, (size_t)wk * 8, (size_t)wk * 8, n_ext, cudaMemcpyDeviceToHost,
                                  ctx->copy_stream[1]));
             CU(cudaEventRecord(down[k], ctx->copy_stream[1]));
         }
@@ -1692,6 +1752,24 @@ extern "C" int glp_synth_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint6
     return GLP_OK;
 }
 
+extern "C" int glp_fib_fill(glp_ctx *ctx, uint64_t *dst, uint64_t nrows, uint64_t ncols)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (!nrows || !ncols) return GLP_OK;
+    if (!dst) return fail(GLP_E_ARG, "glp_fib_fill: dst is NULL");
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = (size_t)nrows * ncols;
+    const bool dev = on_device(dst);
+    gl_t *d = (gl_t *)dst;
+    if (!dev) { GLP(ensure(ctx, ctx->tmp_out, words * sizeof(gl_t))); d = (gl_t *)ctx->tmp_out.p; }
+    const uint64_t nt = ((nrows + GLP_FIB_CHUNK - 1) / GLP_FIB_CHUNK) * ncols;
+    LAUNCH_FLAT(ctx, k_fib_fill, (unsigned)((nt + 127) / 128), 128, d, nrows, ncols);
+    CU(cudaGetLastError());
+    if (!dev) CU(cudaMemcpyAsync(dst, d, words * sizeof(gl_t), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
+}
+
 extern "C" int glp_checksum(glp_ctx *ctx, const uint64_t *src, uint64_t n, uint64_t out[2])
 {
     if (!ctx || !out) return fail(GLP_E_ARG, "glp_checksum: NULL argument");
@@ -1767,10 +1845,20 @@ static int measure_pipe_modes(glp_ctx *ctx, double *ops_per_s, int nmodes)
     CU(cudaEventCreate(&b));
     const unsigned grid = 148 * 8, block = 256;
     const uint32_t iters = 4096;
+    auto go = [&](int mode, uint32_t it) {
+        uint64_t *sink = (uint64_t *)ctx->partial.p;
+        switch (mode) {
+        case 0: LAUNCH_FLAT(ctx, k_int_peak<0>, grid, block, sink, it); break;
+        case 1: LAUNCH_FLAT(ctx, k_int_peak<1>, grid, block, sink, it); break;
+        case 2: LAUNCH_FLAT(ctx, k_int_peak<2>, grid, block, sink, it); break;
+        case 3: LAUNCH_FLAT(ctx, k_int_peak<3>, grid, block, sink, it); break;
+        default: LAUNCH_FLAT(ctx, k_int_peak<4>, grid, block, sink, it); break;
+        }
+    };
     for (int mode = 0; mode < nmodes; mode++) {
-        LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, 64u, mode);      // warm-up
+        go(mode, 64u);                                               // warm-up
         CU(cudaEventRecord(a, ctx->stream));
-        LAUNCH_FLAT(ctx, k_int_peak, grid, block, (uint64_t *)ctx->partial.p, iters, mode);
+        go(mode, iters);
         CU(cudaEventRecord(b, ctx->stream));
         CU(cudaEventSynchronize(b));
         float t = 0;
@@ -1792,3 +1880,8 @@ extern "C" int glp_measure_pipe_peaks(glp_ctx *ctx, double ops_per_s[5])
     if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_pipe_peaks: NULL argument");
     return measure_pipe_modes(ctx, ops_per_s, 5);
 }
+
+// ------------------------------------------------------------------------------------------------
+// several devices, one process (glp_multi_*)
+// ------------------------------------------------------------------------------------------------
+#include "multi.cuh"

@@ -164,6 +164,9 @@ GL_HD gl_t gl_dot_fold(const GlDotAcc &s, GlBorrow &bf)
     return gl_sub(r, l4 << 32);
 }
 
+#ifndef POS_MULADD_FUSED
+#define POS_MULADD_FUSED 0        // 1: gl_mul_add puts c into the accumulator of the a0*b0 IMAD.WIDE
+#endif
 #ifndef POS_MULADD_V2
 #define POS_MULADD_V2 0           // 1: the rank-1 updates of the partial rounds fold with form 2 as well (ptxas then runs out of carry predicates
 #endif                            //    in the partial-round loop and packs them into registers: 548 instead of 388 instructions a round)
@@ -172,6 +175,34 @@ template <bool DEFER>
 GL_HD gl_t gl_mul_add(gl_t a, gl_t b, gl_t c, GlBorrow &bf)
 {
     gl_t lo, hi;
+#if GL_DEVICE_PTX && POS_MULADD_FUSED
+    // c rides in the accumulator of the a0*b0 product (one IMAD.WIDE with carry-out) instead of a 128-bit add afterwards
+    asm("{\n\t"
+        ".reg .u32 a0,a1,b0,b1,c0,c1,x0,x1,s0,s1,s2,y0,y1,z0,z1;\n\t"
+        ".reg .u64 X,Y;\n\t"
+        "mov.b64 {a0,a1}, %2;\n\t"
+        "mov.b64 {b0,b1}, %3;\n\t"
+        "mov.b64 {c0,c1}, %4;\n\t"
+        "mul.wide.u32 Y, a1, b1;\n\t"
+        "mov.b64 {y0,y1}, Y;\n\t"
+        "mad.lo.cc.u32 z0, a0, b0, c0;\n\t"
+        "madc.hi.cc.u32 z1, a0, b0, c1;\n\t"
+        "addc.cc.u32 y0, y0, 0;\n\t"
+        "addc.u32 y1, y1, 0;\n\t"
+        "mul.wide.u32 X, a0, b1;\n\t"
+        "mov.b64 {x0,x1}, X;\n\t"
+        "mad.lo.cc.u32 s0, a1, b0, x0;\n\t"
+        "madc.hi.cc.u32 s1, a1, b0, x1;\n\t"
+        "addc.u32 s2, 0, 0;\n\t"
+        "add.cc.u32 z1, z1, s0;\n\t"
+        "addc.cc.u32 y0, y0, s1;\n\t"
+        "addc.u32 y1, y1, s2;\n\t"
+        "mov.b64 %0, {z0,z1};\n\t"
+        "mov.b64 %1, {y0,y1};\n\t"
+        "}" : "=l"(lo), "=l"(hi) : "l"(a), "l"(b), "l"(c));
+    if (DEFER) return gl_reduce128_defer_t<POS_MULADD_V2 != 0>(lo, hi, bf);
+    return gl_reduce128_m<POS_MULADD_MODE>(lo, hi);
+#endif
     if (POS_MUL4W) gl_mul_wide4(a, b, lo, hi);
     else gl_mul_wide(a, b, lo, hi);
 #if GL_DEVICE_PTX
@@ -526,7 +557,7 @@ GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf)
                 gl_dot_init(acc);
 #pragma unroll
                 for (int i = 0; i < 12; i++) gl_dot_mac(acc, x[i], S[i]);
-                if (DEFER && GL_BORROW_MIN && !POS_MUL4W) {
+                if (DEFER && GL_BORROW_MIN && !POS_MUL4W && !POS_MULADD_FUSED) {
 #pragma unroll
                     for (int i = 1; i < 11; i += 2) gl_mul_add2_defer(x[0], S[11 + i], S[12 + i], x[i], x[i + 1], bf);
                     x[11] = gl_mul_add<DEFER>(x[0], S[22], x[11], bf);
