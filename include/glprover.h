@@ -175,6 +175,12 @@ int glp_multi_merkletree(glp_multi *m, uint64_t *tree, const uint64_t *in, uint6
 int glp_multi_commit(glp_multi *m, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in, uint64_t n,
                      uint64_t n_ext, uint64_t ncols);
 
+/* One step of the above for callers that run one process per GPU (xlayer_prover_b200/sharded.py): copy the levels of this
+ * rank's subtree (sub_rows leaves, level-major) into their slices of the full level-major tree of sub_rows * nparts leaves at
+ * `tree` -- typically rank 0's buffer mapped with glp_ipc_import.  STREAM ORDERED: queued on the context's stream, not
+ * synchronised; the caller fences the ranks before the top levels are hashed (glp_merkle_levels on the nparts subtree roots). */
+int glp_place_subtree(glp_ctx *ctx, uint64_t *tree, const uint64_t *subtree, uint64_t sub_rows, uint32_t nparts, uint32_t part);
+
 /* ---- the callers either side of the commit ---- */
 /* Step 4 of Starks::genProof, the quotient commit (src/starkpil/starks.cpp:261-291):
  *   qq1 = INTT_{n_ext}(q)  (q: n_ext x qdim);  qq2[k][p*qdim+d] = qq1[p*n+k][d] * shift^(-n*p)  (k < n, p < qdeg);

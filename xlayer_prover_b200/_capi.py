@@ -70,6 +70,7 @@ SIGNATURES = {
     "glp_get_profile": (i32, [vp, C.POINTER(C.c_float), C.POINTER(u32)]),
     "glp_measure_int_peak": (i32, [vp, C.POINTER(C.c_double)]),
     "glp_measure_pipe_peaks": (i32, [vp, C.POINTER(C.c_double)]),
+    "glp_place_subtree": (i32, [vp, vp, vp, u64, u32, u32]),
     "glp_multi_init": (i32, [i32, C.POINTER(i32), C.POINTER(vp)]),
     "glp_multi_destroy": (None, [vp]),
     "glp_multi_device_count": (i32, [vp]),
@@ -260,6 +261,10 @@ class Context:
 
     def merkle_group_proof(self, proof, source, nodes, width, height, idx):
         self.lib.check(self.lib.glp_merkle_group_proof(self.h, ptr_of(proof), ptr_of(source), ptr_of(nodes), width, height, idx))
+
+    def place_subtree(self, tree, subtree, sub_rows, nparts, part):
+        """queue the copies of this rank's subtree levels into their slices of the full tree (stream ordered, not synchronised)"""
+        self.lib.check(self.lib.glp_place_subtree(self.h, ptr_of(tree), ptr_of(subtree), sub_rows, nparts, part))
 
     def merkle_group_proofs(self, proofs, source, nodes, width, height, idx):
         """getGroupProof for every index of `idx` (a host uint64 array) in one launch / one download"""

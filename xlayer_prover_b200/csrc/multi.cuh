@@ -99,6 +99,17 @@ uint64_t multi_top_offset(uint64_t R, unsigned G)           // word offset of th
 }
 }  // namespace
 
+// The placement step on its own, for the one-process-per-GPU path (sharded.py): rank `part` of `nparts` copies the levels of its
+// subtree (sub_rows leaves) into their slices of the full tree, which may be rank 0's buffer mapped over CUDA IPC.  Stream
+// ordered: the copies are queued on the context's stream and the call returns; the caller fences the ranks.
+extern "C" int glp_place_subtree(glp_ctx *ctx, uint64_t *tree, const uint64_t *subtree, uint64_t sub_rows, uint32_t nparts, uint32_t part)
+{
+    if (!ctx || !tree || !subtree) return fail(GLP_E_ARG, "glp_place_subtree: NULL argument");
+    if (!is_pow2(sub_rows) || !is_pow2(nparts) || part >= nparts) return fail(GLP_E_ARG, "glp_place_subtree: bad shape");
+    CU(cudaSetDevice(ctx->device));
+    return multi_place_subtree(ctx, tree, (const gl_t *)subtree, sub_rows, nparts, part, ctx->stream);
+}
+
 extern "C" int glp_multi_init(int ndev, const int *devs, glp_multi **out)
 {
     if (!out) return fail(GLP_E_ARG, "glp_multi_init: NULL argument");

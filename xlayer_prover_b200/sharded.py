@@ -13,8 +13,10 @@ exactly as BASELINE.json's north_star prescribes:
      slabs (CUDA IPC over NVLink) and the LDE's last NTT pass stores each tile straight into the owner's slab at this
      rank's column offset (glp_extend_pol_scatter) -- no all-to-all, no receive buffer, no interleave pass; the only
      collective left is a one-word all-reduce that orders the peers' stores before the hashing;
-  4. the G subtrees are gathered on rank 0, re-laid level-major into the reference's `nodes` layout
-     (poseidon_goldilocks.cpp:283-300) and the top log2(G) levels are hashed there (glp_merkle_levels).
+  4. every rank copies the levels of its subtree straight into their slices of the reference's level-major `nodes` layout
+     (poseidon_goldilocks.cpp:283-300) in rank 0's tree, mapped over CUDA IPC (glp_place_subtree: ~25 peer copies, no gather,
+     no re-layout pass), and rank 0 hashes the top log2(G) levels (glp_merkle_levels).  The unfused path (gloo tests) gathers
+     the subtrees and re-lays them on rank 0.
 
 torch is plumbing only: it owns the buffers, the NCCL communicator and the current stream; all arithmetic
 is in libglprover.so.  Results are identical for every G (tests/test_sharded.py).
@@ -96,6 +98,18 @@ class ShardedCommit:
         self.parts = [self.slab_ptr if g == self.rank else self.ctx.ipc_import(handles[g]) for g in range(G)]
         self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.ext_cols = self.recv = None
+        # the full tree lives on rank 0 (cudaMalloc, exported); every rank maps it and writes its subtree's levels straight
+        # into their slices of the reference's level-major layout (glp_place_subtree) -- no gather, no re-layout pass
+        nt = tree_num_elements(self.n_ext)
+        handle = [None]
+        if self.rank == 0:
+            self.tree_ptr = self.ctx.device_alloc(8 * nt)
+            handle[0] = self.ctx.ipc_export(self.tree_ptr)
+        dist.broadcast_object_list(handle, src=0, group=self.group)
+        if self.rank != 0:
+            self.tree_ptr = self.ctx.ipc_import(handle[0])
+        self._tree_view = _tensor_from_ptr(self.tree_ptr, nt, self.device) if self.rank == 0 else None
+        self._entry_fence = True
 
     def close(self):
         if getattr(self, "fused", False) and getattr(self, "parts", None):
@@ -106,8 +120,14 @@ class ShardedCommit:
             for g, p in enumerate(self.parts):
                 if g != self.rank:
                     self.ctx.ipc_close(p)
-            self.slab = None
+            if self.rank != 0:
+                self.ctx.ipc_close(self.tree_ptr)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)           # rank 0 frees the tree after everyone has unmapped it
+            self.slab = self.tree = self._tree_view = None
             self.ctx.device_free(self.slab_ptr)
+            if self.rank == 0:
+                self.ctx.device_free(self.tree_ptr)
             self.parts = None
 
     def _fence(self):
@@ -122,7 +142,9 @@ class ShardedCommit:
     def extend(self, in_slice, in_pitch=None):
         """Step 1: LDE of my column slice.  in_slice: [n x w] (pitch in_pitch, default dense)."""
         if self.fused:
-            self._fence()                       # every rank has finished reading its slab (the previous commit's hashing)
+            if self._entry_fence:               # every rank has finished reading its slab; after a complete commit the tree fence
+                self._fence()                   # of finish() has already said so
+            self._entry_fence = True
             if self.w:
                 self.ctx.extend_pol_scatter(self.parts, self.ncols, self.c0, in_slice, in_pitch or self.w, self.n_ext, self.n, self.w)
             return
@@ -157,6 +179,19 @@ class ShardedCommit:
         G = self.world
         if G == 1:
             self.tree = self.subtree
+            return self.tree[-4:].clone()
+        if self.fused:
+            self.ctx.place_subtree(self.tree_ptr, self.subtree, self.R, G, self.rank)
+            self._fence()                       # every subtree's levels are in rank 0's tree; every rank is done with its slab
+            self._entry_fence = False
+            if self.rank != 0:
+                return None
+            self.tree = self._tree_view
+            off_top, nn = 0, self.n_ext
+            while nn > G:
+                off_top += 4 * nn
+                nn //= 2
+            self.ctx.merkle_levels(self.tree[off_top:], G)
             return self.tree[-4:].clone()
         gathered = [torch.empty_like(self.subtree) for _ in range(G)] if self.rank == 0 else None
         dist.gather(self.subtree, gathered, dst=0, group=self.group)
