@@ -182,52 +182,9 @@ int ref_quotient_commit(uint64_t *cm4, uint64_t *tree, uint64_t *q_2ns, uint64_t
     return 0;
 }
 
-// ---- the constant tree as bctree lays it out (tools/starkpil/bctree/build_const_tree.cpp:531-575): header
-// [nPols, nExt], the extended constant polynomials, the Merkle nodes.  bctree's own `interpolate` (:398-470) is the
-// same map as NTT_Goldilocks::extendPol (INTT, * shift^i / N, zero-padded NTT), which is what is called here. ----
-int ref_const_tree(uint64_t *const_tree, uint64_t *const_pols, uint64_t n, uint64_t n_ext, uint64_t npols)
-{
-    NTT_Goldilocks ntt(n);
-    std::vector<E> buffer(n_ext * npols);
-    const_tree[0] = npols;
-    const_tree[1] = n_ext;
-    ntt.extendPol((E *)const_tree + 2, (E *)const_pols, n_ext, n, npols, buffer.data());
-    PoseidonGoldilocks::merkletree((E *)const_tree + 2 + npols * n_ext, (E *)const_tree + 2, npols, n_ext);
-    return 0;
-}
+// The constant tree (bctree) and the FRI folding step are NOT restated here: oracle/_ref/libbctree.so and libfriref.so are the
+// reference's own build_const_tree.cpp and friProve.cpp compiled where they lie (oracle/ref_bctree_capi.cpp, ref_fri_capi.cpp).
 
-// ---- one FRI folding step as FRIProve::prove runs it for si > 0 (src/starkpil/fri/friProve.cpp:22-108): for every
-// g < pol2N = 2^nBitsStep the nX = 2^(polBits - nBitsStep) values friPol[i*pol2N + g] are interpolated (INTT, :102),
-// coefficient i is scaled by sinv_g^i with sinv_g = shiftInv * w(polBits)^(-g) (polMulAxi, :103,192-200; the per-thread
-// start values of :62-83 are exactly that product) and the polynomial is evaluated at special_x (evalPol, :104,201-217).
-// Polinomial itself needs the prover's logging tree, so its three-word elements are addressed directly. ----
-int ref_fri_fold(uint64_t *pol2_e, uint64_t *friPol, uint64_t polBits, uint64_t nBitsStep, uint64_t *special_x, uint64_t shiftInv)
-{
-    const uint64_t reductionBits = polBits - nBitsStep, pol2N = 1ull << nBitsStep, nX = 1ull << reductionBits;
-    E wi = Goldilocks::inv(Goldilocks::w(polBits));
-    E sinv_{shiftInv};
-    NTT_Goldilocks ntt(nX, 1);
-    std::vector<E> ppar(nX * 3), ppar_c(nX * 3);
-    for (uint64_t g = 0; g < pol2N; g++) {
-        for (uint64_t i = 0; i < nX; i++) std::memcpy(&ppar[i * 3], friPol + ((i * pol2N) + g) * 3, 3 * sizeof(E));
-        ntt.INTT(ppar_c.data(), ppar.data(), nX, 3);
-        E r = Goldilocks::one();
-        for (uint64_t i = 0; i < nX; i++) {
-            Goldilocks3::mul((Goldilocks3::Element &)ppar_c[i * 3], (Goldilocks3::Element &)ppar_c[i * 3], r);
-            r = r * sinv_;
-        }
-        Goldilocks3::Element res;
-        std::memcpy(res, &ppar_c[(nX - 1) * 3], sizeof res);
-        for (int64_t i = (int64_t)nX - 2; i >= 0; i--) {
-            Goldilocks3::Element aux;
-            Goldilocks3::mul(aux, res, (Goldilocks3::Element &)*(E *)special_x);
-            Goldilocks3::add(res, aux, (Goldilocks3::Element &)ppar_c[i * 3]);
-        }
-        std::memcpy(pol2_e + g * 3, res, sizeof res);
-        sinv_ = sinv_ * wi;
-    }
-    return 0;
-}
 // ---- the FRI layer tree (friProve.cpp:110-123,252-270): getTransposed regroups the folded polynomial into
 // nGroups = 2^nextBits rows of groupSize = polN / nGroups extension elements, MerkleTreeGL hashes the rows. ----
 int ref_fri_group_tree(uint64_t *aux, uint64_t *tree, uint64_t *pol, uint64_t polN, uint64_t nextBits)

@@ -186,8 +186,6 @@ class RefLib(_Lib):
         L.ref_mt_get_group_proof.restype, L.ref_mt_get_group_proof.argtypes = None, [vp, u64p, u64]
 
         L.ref_quotient_commit.restype, L.ref_quotient_commit.argtypes = C.c_int, [u64p, u64p, u64p, u64, u64, u64, u64]
-        L.ref_const_tree.restype, L.ref_const_tree.argtypes = C.c_int, [u64p, u64p, u64, u64, u64]
-        L.ref_fri_fold.restype, L.ref_fri_fold.argtypes = C.c_int, [u64p, u64p, u64, u64, u64p, u64]
         L.ref_fri_group_tree.restype, L.ref_fri_group_tree.argtypes = C.c_int, [u64p, u64p, u64p, u64, u64]
         L.ref_tr_new.restype, L.ref_tr_new.argtypes = vp, []
         L.ref_tr_free.restype, L.ref_tr_free.argtypes = None, [vp]
@@ -205,21 +203,98 @@ class RefLib(_Lib):
         self.lib.ref_quotient_commit(_ptr(cm4), _ptr(tree), _ptr(q.copy()), n, n_ext, qdim, qdeg)
         return self.canonical(cm4), self.canonical(tree)
 
-    def const_tree(self, const_pols, n_ext):
-        """bctree's *.consttree words [nPols, nExt, extended pols, nodes] (build_const_tree.cpp:555-575), canonical."""
+    # ---- the reference's constant-tree builder and FRI prover, compiled from their own sources (oracle/_ref/libbctree.so,
+    # libfriref.so; oracle/Makefile): no arithmetic of theirs is restated on this side
+    def _bct(self):
+        if getattr(self, "_bctlib", None) is None:
+            L = C.CDLL(os.path.join(os.path.dirname(self.path), "libbctree.so"))
+            L.ref_bctree_interpolate.restype, L.ref_bctree_interpolate.argtypes = C.c_int, [u64p, u64p, C.c_uint64, C.c_uint64, C.c_uint64]
+            L.ref_bctree_build.restype, L.ref_bctree_build.argtypes = C.c_int, [C.c_char_p] * 4
+            self._bctlib = L
+        return self._bctlib
+
+    def _fri(self):
+        if getattr(self, "_frilib", None) is None:
+            L = C.CDLL(os.path.join(os.path.dirname(self.path), "libfriref.so"))
+            u64 = C.c_uint64
+            L.ref_fri_fold_step.restype, L.ref_fri_fold_step.argtypes = C.c_int, [u64p, u64p, u64, u64, u64p, u64]
+            L.ref_fri_prove.restype = C.c_int
+            L.ref_fri_prove.argtypes = [u64p, u64, u64p, u64, u64, C.POINTER(u64p), u64p, u64p, u64, u64p, u64p, u64p, u64p, u64, u64p]
+            self._frilib = L
+        return self._frilib
+
+    def bctree_interpolate(self, const_pols, n_ext):
+        """bctree's own `interpolate` (tools/starkpil/bctree/build_const_tree.cpp:398-531): [n x npols] -> [n_ext x npols], canonical"""
         a = np.ascontiguousarray(const_pols, dtype=np.uint64)
         n, npols = a.shape
-        out = np.zeros(2 + npols * n_ext + self._tree_num_elements(n_ext), dtype=np.uint64)
-        self.lib.ref_const_tree(_ptr(out), _ptr(a.copy()), n, n_ext, npols)
+        out = np.zeros((n_ext, npols), dtype=np.uint64)
+        with self._at_least_two_threads():
+            self._bct().ref_bctree_interpolate(_ptr(out), _ptr(a.copy()), npols, n.bit_length() - 1, n_ext.bit_length() - 1)
         return self.canonical(out)
 
+    def _at_least_two_threads(self):
+        """bctree divides by omp_get_max_threads() / 2 (build_const_tree.cpp:408,370): with one OpenMP thread that is a division by zero"""
+        import contextlib
+
+        @contextlib.contextmanager
+        def cm():
+            t = self.max_threads()
+            if t < 2:
+                self.set_threads(2)
+            try:
+                yield
+            finally:
+                if t < 2:
+                    self.set_threads(t)
+        return cm()
+
+    def bctree_build(self, const_file, stark_struct_file, const_tree_file, ver_key_file):
+        """buildConstTree (build_const_tree.cpp:533-600): the files bctree reads and writes"""
+        with self._at_least_two_threads():
+            self._bct().ref_bctree_build(*(os.fsencode(f) for f in (const_file, stark_struct_file, const_tree_file, ver_key_file)))
+
+    def const_tree(self, const_pols, n_ext):
+        """bctree's *.consttree words [nPols, nExt, extended pols, nodes] (build_const_tree.cpp:555-575), canonical: bctree's
+        interpolate, then the reference's merkletree, as buildConstTree strings them together (:545-575)."""
+        a = np.ascontiguousarray(const_pols, dtype=np.uint64)
+        n, npols = a.shape
+        ext = self.bctree_interpolate(a, n_ext)
+        return np.concatenate([np.array([npols, n_ext], dtype=np.uint64), ext.reshape(-1), self.merkletree(ext)])
+
     def fri_fold(self, pol, pol_bits, step_bits, special_x, shift_inv):
-        """one folding step of FRIProve::prove (friProve.cpp:22-108); pol [2^pol_bits x 3] -> [2^step_bits x 3], canonical"""
+        """one folding step with the reference's own INTT, FRIProve::polMulAxi and FRIProve::evalPol (friProve.cpp:93-105,192-217)"""
         pol = np.ascontiguousarray(pol, dtype=np.uint64)
         out = np.zeros((1 << step_bits, 3), dtype=np.uint64)
         x = np.ascontiguousarray(special_x, dtype=np.uint64)
-        self.lib.ref_fri_fold(_ptr(out), _ptr(pol.copy()), pol_bits, step_bits, _ptr(x), int(shift_inv))
+        self._fri().ref_fri_fold_step(_ptr(out), _ptr(pol.copy()), pol_bits, step_bits, _ptr(x), int(shift_inv))
         return self.canonical(out)
+
+    def fri_prove(self, fri_pol, pol_bits, step_bits, nqueries, trees_src, seed):
+        """FRIProve::prove itself (friProve.cpp:5-190) on friPol [2^pol_bits x 3] and the five stage trees whose sources are
+        trees_src[i] [2^pol_bits x w_i]; the transcript holds `seed` when it starts.  Returns what it left in the FRIProof:
+        roots of the layer trees, the last polynomial, and the query proofs flattened in the order queryPol pushed them."""
+        pol = np.ascontiguousarray(fri_pol, dtype=np.uint64).copy()
+        srcs = [np.ascontiguousarray(t, dtype=np.uint64) for t in trees_src]
+        assert len(srcs) == 5 and all(t.shape[0] == 1 << pol_bits for t in srcs)
+        widths = np.array([t.shape[1] for t in srcs], dtype=np.uint64)
+        ptrs = (u64p * 5)(*[_ptr(t) for t in srcs])
+        steps = np.array(step_bits, dtype=np.uint64)
+        seed = np.ascontiguousarray(seed, dtype=np.uint64)
+        roots = np.zeros((max(0, len(step_bits) - 1), 4), dtype=np.uint64)
+        final = np.zeros((1 << step_bits[-1], 3), dtype=np.uint64)
+        ys = np.zeros(nqueries, dtype=np.uint64)
+        cap = 0
+        for si, nb in enumerate(step_bits):
+            if si == 0:
+                cap += nqueries * sum(int(w) + 4 * pol_bits for w in widths)
+            else:
+                cap += nqueries * (3 * (1 << (step_bits[si - 1] - nb)) + 4 * nb)
+        q = np.zeros(cap, dtype=np.uint64)
+        used = C.c_uint64(0)
+        rc = self._fri().ref_fri_prove(_ptr(pol), pol_bits, _ptr(steps), len(step_bits), nqueries, ptrs, _ptr(widths), _ptr(seed), seed.size,
+                                       _ptr(roots.reshape(-1)) if roots.size else None, _ptr(final.reshape(-1)), _ptr(ys), _ptr(q), cap, C.byref(used))
+        assert rc == 0 and used.value == cap, (rc, used.value, cap)
+        return {"roots": roots, "final": final, "queries": q}
 
     def fri_group_tree(self, pol, next_bits):
         """getTransposed + MerkleTreeGL of a FRI layer (friProve.cpp:110-123,252-270); returns (aux, tree), canonical"""

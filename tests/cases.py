@@ -3,6 +3,8 @@
 The generators restate the input loops of the reference's own tests
 (src/goldilocks/tests/tests.cpp: Fibonacci vectors :1597-1610, :1747-1760; column-Fibonacci matrices
 :1817-1835, :2260-2275) so the known answers in tests/golden/kat.json apply."""
+import os
+
 import numpy as np
 
 P = 0xFFFFFFFF00000001
@@ -257,6 +259,30 @@ def check_const_tree(ctx, reference, rng, shapes=((16, 2, 5), (64, 4, 21), (8, 2
         root = np.zeros(4, dtype=np.uint64)
         mt.getRoot(root)
         check_equal(root, want[-4:], "constRoot")
+    check_const_tree_files(ctx, reference, rng)
+
+
+def check_const_tree_files(ctx, reference, rng, n=64, n_ext=128, npols=9):
+    """The artefacts themselves: bctree's buildConstTree (build_const_tree.cpp:533-600, compiled from the reference) reads a
+    constant-polynomials file and a starkStruct json and writes the *.consttree image and the verification key; the image
+    glp_const_tree produces from the same polynomials must be byte-identical (after canonicalisation) and carry that root."""
+    import json
+    import tempfile
+    from xlayer_prover_b200 import build_const_tree
+    a = edge_matrix(rng, n, npols) % np.uint64(P)                       # what a .const file holds: canonical words, row-major
+    with tempfile.TemporaryDirectory() as d:
+        cf, sf, tf, vf = (os.path.join(d, x) for x in ("x.const", "x.starkstruct.json", "x.consttree", "x.verkey.json"))
+        a.tofile(cf)
+        with open(sf, "w") as f:
+            json.dump({"nBits": n.bit_length() - 1, "nBitsExt": n_ext.bit_length() - 1, "nQueries": 8, "verificationHashType": "GL",
+                       "steps": [{"nBits": n_ext.bit_length() - 1}, {"nBits": 3}]}, f)
+        reference.bctree_build(cf, sf, tf, vf)
+        image = reference.canonical(np.fromfile(tf, dtype=np.uint64))
+        with open(vf) as f:
+            verkey = json.load(f)
+    got = build_const_tree(a, n.bit_length() - 1, n_ext.bit_length() - 1, ctx=ctx)
+    check_equal(got, image, "*.consttree image written by the reference's bctree")
+    check_equal(got[-4:], np.array(verkey["constRoot"], dtype=np.uint64), "constRoot of the verification key")
 
 
 def check_transcript(ctx, reference, rng):
@@ -406,3 +432,74 @@ def check_group_proofs(ctx, reference, rng, device=True, shapes=((256, 21), (1 <
             ctx.device_free(dsrc)
             ctx.device_free(dnodes)
         del canon
+
+
+def check_fri_prove(ctx, reference, rng, pol_bits=9, steps=(9, 6, 3), nq=6, widths=(5, 3, 9, 6, 2)):
+    """The reference's WHOLE FRIProve::prove (src/starkpil/fri/friProve.cpp:5-190, compiled from the reference with its own
+    Polinomial, FRIProof, Transcript and MerkleTreeGL: oracle/_ref/libfriref.so) against the same protocol driven through this
+    library with every polynomial and tree on the device: challenges from the transcript, glp_fri_fold per layer, the layer trees
+    (glp_fri_group_tree), the query indices (getPermutations) and ALL query proofs of every tree in one glp_merkle_group_proofs
+    call per tree.  Compared: every layer root, the last polynomial, and every word of every proof in the order queryPol emits
+    them."""
+    from xlayer_prover_b200 import Transcript
+    n = 1 << pol_bits
+    fri_pol = edge_matrix(rng, n, 3)
+    srcs = [edge_matrix(rng, n, w) for w in widths]
+    seed = rng.integers(0, P, size=11, dtype=np.uint64)
+    want = reference.fri_prove(fri_pol, pol_bits, list(steps), nq, srcs, seed)
+    # ---- ours ----
+    tr = Transcript(ctx=ctx)
+    tr.put(seed)
+    dsrc = [ctx.to_device(t) for t in srcs]
+    dtrees = []
+    for t, d in zip(srcs, dsrc):
+        dt = ctx.device_alloc(8 * tree_words(n))
+        ctx.merkletree(dt, d, t.shape[1], n)
+        dtrees.append(dt)
+    dpol, bits, shift_inv = ctx.to_device(fri_pol), pol_bits, pow(7, P - 2, P)
+    frees, layers, roots = [dpol] + dsrc + dtrees, [], []
+    for si, nb in enumerate(steps):
+        x = tr.getField()
+        if si > 0 or nb != bits:
+            dnew = ctx.device_alloc(8 * 3 << nb)
+            ctx.fri_fold(dnew, dpol, bits, nb, x, shift_inv)
+            frees.append(dnew)
+            dpol = dnew
+        if si + 1 < len(steps):
+            nxt = steps[si + 1]
+            daux, dlt = ctx.device_alloc(8 * 3 << nb), ctx.device_alloc(8 * tree_words(1 << nxt))
+            root = ctx.fri_group_tree(daux, dlt, dpol, nb, nxt)
+            tr.put(root)
+            roots.append(root)
+            layers.append((daux, dlt, 1 << nxt, 3 << (nb - nxt)))
+            frees += [daux, dlt]
+        else:
+            final = ctx.to_host(dpol, (1 << nb, 3))
+            tr.put(final.reshape(-1))
+        for _ in range(bits - nb):
+            shift_inv = shift_inv * shift_inv % P
+        bits = nb
+    check_equal(np.array(roots, dtype=np.uint64).reshape(-1, 4), want["roots"], "FRI layer roots against FRIProve::prove")
+    check_equal(final, want["final"], "last FRI polynomial against FRIProve::prove")
+    ys = np.array(tr.getPermutations(nq, steps[0]), dtype=np.uint64)
+    out = []
+    for si in range(len(steps)):
+        if si == 0:
+            per_tree = []
+            for t, d, dt in zip(srcs, dsrc, dtrees):
+                w = t.shape[1]
+                pr = np.zeros((nq, w + 4 * pol_bits), dtype=np.uint64)
+                ctx.merkle_group_proofs(pr, d, dt, w, n, ys)
+                per_tree.append(pr)
+            for i in range(nq):                                   # queryPol(treesGL[5], ys[i]): the five trees' proofs of one index together
+                out += [pr[i] for pr in per_tree]
+        else:
+            daux, dlt, h, w = layers[si - 1]
+            pr = np.zeros((nq, w + 4 * (h.bit_length() - 1)), dtype=np.uint64)
+            ctx.merkle_group_proofs(pr, daux, dlt, w, h, ys)
+            out += [pr[i] for i in range(nq)]
+        if si + 1 < len(steps):
+            ys = ys % np.uint64(1 << steps[si + 1])
+    check_equal(np.concatenate(out), want["queries"], "every query proof against FRIProve::prove")
+    for p in frees:
+        ctx.device_free(p)

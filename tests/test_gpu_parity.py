@@ -647,6 +647,13 @@ def test_group_proofs_batched(ctx, reference, rng):
     check_group_proofs(ctx, reference, rng, shapes=((256, 21), (1 << 12, 3), (64, 128), (2, 5), (1, 9), (1 << 16, 40)))
 
 
+def test_fri_prove_whole(ctx, reference, rng):
+    """FRIProve::prove (the reference's own, compiled: oracle/_ref/libfriref.so) against the device-resident FRI flow"""
+    from cases import check_fri_prove
+    check_fri_prove(ctx, reference, rng, pol_bits=14, steps=(14, 10, 6, 3), nq=16, widths=(40, 12, 21, 6, 3))
+    check_fri_prove(ctx, reference, rng, pol_bits=9, steps=(9, 3), nq=5)
+
+
 # ---------------------------------------------------------------- several devices
 def test_multi_contexts_on_one_device(oracle, rng):
     """glp_multi_* with G = 2 and 4 contexts on device 0 (a host thread each, the slabs in the same memory): the split, the

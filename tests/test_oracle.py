@@ -113,3 +113,24 @@ def test_port_vs_reference_random(port, reference):
 
 def test_tree_words():
     assert tree_words(64) == 508
+
+
+def test_reference_bctree_interpolate_is_extend_pol(reference):
+    """tools/starkpil/bctree/build_const_tree.cpp:398-531 (`interpolate`, compiled from the reference into
+    oracle/_ref/libbctree.so) and NTT_Goldilocks::extendPol are the same map -- which is why glp_const_tree may be glp_commit
+    writing into the *.consttree layout.  Checked here on the reference's two implementations, not asserted in a comment."""
+    rng = np.random.default_rng(5)
+    for n, n_ext, npols in ((16, 32, 5), (64, 256, 3), (1 << 13, 1 << 14, 2), (8, 16, 1)):
+        a = rng.integers(0, 0xFFFFFFFF00000001, size=(n, npols), dtype=np.uint64)
+        assert np.array_equal(reference.bctree_interpolate(a, n_ext), reference.extend_pol(a, n_ext)), (n, n_ext, npols)
+
+
+def test_reference_fri_fold_helpers_against_first_principles(reference):
+    """FRIProve::polMulAxi / evalPol around the reference INTT (oracle/_ref/libfriref.so), on a fold whose answer is known in
+    closed form: a polynomial of degree < nX per coset folds to its evaluation -- here friPol = evaluations of the constant
+    polynomial c on the domain, so every folded value is c whatever special_x is."""
+    P = 0xFFFFFFFF00000001
+    pol = np.zeros((1 << 6, 3), dtype=np.uint64)
+    pol[:] = np.array([5, 7, 11], dtype=np.uint64)
+    out = reference.fri_fold(pol, 6, 3, np.array([123, 456, 789], dtype=np.uint64), pow(7, P - 2, P))
+    assert np.array_equal(out, np.tile(np.array([5, 7, 11], dtype=np.uint64), (8, 1)))
