@@ -83,7 +83,10 @@ int glp_ntt_live(glp_ctx *ctx, uint64_t *dst, const uint64_t *src, uint64_t size
  * P_c interpolates in[:,c] on the size-n subgroup.  out may alias in. */
 int glp_extend_pol(glp_ctx *ctx, uint64_t *out, const uint64_t *in, uint64_t n_ext, uint64_t n, uint64_t ncols);
 /* Same on a column window: reads in[i*in_pitch + c], writes out[i*out_pitch + c], c < ncols.  This is the unit
- * of the multi-GPU path (each rank extends its own column slice; north_star / SURVEY 8e). */
+ * of the unfused multi-GPU path (each rank extends its own column slice; north_star / SURVEY 8e).  Device pointers only.
+ * STREAM ORDERED: unlike every other compute entry point this one does NOT synchronise -- the kernels are queued on the
+ * context's stream (glp_set_stream) and the call returns; read `out` from that stream, or after glp_synchronize.  It always
+ * runs the exact NTT passes (never the optimistic ones, which need a host check of their flag). */
 int glp_extend_pol_pitched(glp_ctx *ctx, uint64_t *out, uint64_t out_pitch, const uint64_t *in, uint64_t in_pitch,
                            uint64_t n_ext, uint64_t n, uint64_t ncols);
 /* The same extension with its OUTPUT row-sharded: row i of the result (i < n_ext) is written to

@@ -63,6 +63,52 @@ def permute(T, x):
     return mat(x, M)
 
 
+def spw(T, dmax=7):
+    """Partial rounds taken M at a time (poseidon.cuh POS_PR_CHUNK): the rank-1 updates x_i += y_j * v_i(j) of a chunk are
+    deferred to its end, so the dot product of round k picks up y_j * W for every earlier round j of the chunk, with
+    W = sum_{i>=1} v_i(j) * S_i(k).  W turns out to depend on d = k - j only and to be SMALL (13, 21, 29, ... bits: entries of
+    powers of the MDS matrix) -- both facts are asserted here, the kernels rely on them."""
+    S = T["S"]
+    out = []
+    for d in range(1, dmax + 1):
+        vals = {sum(S[23 * j + 11 + i] * S[23 * (j + d) + i] for i in range(1, 12)) % P for j in range(0, 22 - d)}
+        assert len(vals) == 1, d
+        out.append(vals.pop())
+    assert all(S[23 * r] == 25 for r in range(22))       # the diagonal weight of every partial round is M[0][0] = 17 + 8
+    assert out[0] < 2 ** 32 and out[1] < 2 ** 32 and out[2] < 2 ** 32
+    return out
+
+
+def permute_chunked(T, x, m=4):
+    """permute() with the partial rounds taken m at a time (then the remaining 22 % m), as the kernels do -- checked against permute()"""
+    C, M, Pm, S = T["C"], T["M"], T["P"], T["S"]
+    W = spw(T)
+    x = [(a + c) % P for a, c in zip(x, C[:12])]
+    def mat(x, A): return [sum(A[j * 12 + i] * x[j] for j in range(12)) % P for i in range(12)]
+    for r in range(3):
+        x = [(pow(a, 7, P) + C[12 * (r + 1) + i]) % P for i, a in enumerate(x)]
+        x = mat(x, M)
+    x = [(pow(a, 7, P) + C[48 + i]) % P for i, a in enumerate(x)]
+    x = mat(x, Pm)
+    r = 0
+    while r < 22:
+        mm = min(m, 22 - r)
+        ys, x0 = [], x[0]
+        for k in range(mm):
+            y = (pow(x0, 7, P) + C[60 + r + k]) % P
+            ys.append(y)
+            x0 = (25 * y + sum(x[i] * S[23 * (r + k) + i] for i in range(1, 12)) + sum(ys[j] * W[k - j - 1] for j in range(k))) % P
+        for i in range(1, 12):
+            x[i] = (x[i] + sum(ys[k] * S[23 * (r + k) + 11 + i] for k in range(mm))) % P
+        x[0] = x0
+        r += mm
+    for r in range(3):
+        x = [(pow(a, 7, P) + C[82 + 12 * r + i]) % P for i, a in enumerate(x)]
+        x = mat(x, M)
+    x = [pow(a, 7, P) for a in x]
+    return mat(x, M)
+
+
 def fmt(vals, per=4):
     lines = []
     for i in range(0, len(vals), per):
@@ -84,6 +130,8 @@ def main():
     got = permute(T, fib)
     assert got[0] == 0x3095570037F4605D and got[11] == 0xF58A41D4028C66A5, hex(got[0])
     assert permute(T, [0] * 12)[0] == 0x3C18A9786CB0B359
+    for m in (2, 3, 4, 7):
+        assert permute_chunked(T, fib, m) == got and permute_chunked(T, list(range(5, 17)), m) == permute(T, list(range(5, 17))), m
     rcf = T["C"][12:60] + T["C"][82:118] + [0] * 12
     mrc = []
     for r in range(8):
@@ -116,6 +164,10 @@ def main():
           "#define GLP_POSEIDON_MRCL_INIT \\\n" + "\n".join("    " + ", ".join("0x%xu" % v for v in mrcl[i:i + 12]) + "," for i in range(0, len(mrcl), 12)).replace("\n", " \\\n"), "",
           "// MRCD[(r*12+i)*2 + h] = 2^52 + (32-bit half h of MRC[r*12+i]) as a double: the start value of the FP64 MDS chains",
           "#define GLP_POSEIDON_MRCD_INIT \\\n" + "\n".join("    " + ", ".join("%d.0" % (2 ** 52 + h) for v in mrc[i:i + 2] for h in (v & 0xFFFFFFFF, v >> 32)) + "," for i in range(0, len(mrc), 2)).replace("\n", " \\\n"), "",
+          "// SPW[d-1] = sum_{i=1..11} SP[23j + 11 + i] * SP[23(j+d) + i] mod p (the same for every j): the weight the S-box output of\n"
+          "// partial round j gets in the dot product of round j+d when the rank-1 updates of rounds j..j+d-1 are still deferred\n"
+          "// (POS_PR_CHUNK, poseidon.cuh).  13, 21, 29, 36, ... bits.  SP[23j] (the diagonal weight) is 25 in every round.",
+          "#define GLP_POSEIDON_SPW_INIT " + ", ".join("0x%xULL" % v for v in spw(T)), "#define GLP_POSEIDON_SP_DIAG 25", "",
           "#define GLP_MDS_CIRC_INIT " + ", ".join(str(v) for v in circ),
           "#define GLP_MDS_DIAG0 8", ""]
     open(os.path.join(ROOT, "xlayer_prover_b200/csrc/poseidon_tables.cuh"), "w").write("\n".join(cu))

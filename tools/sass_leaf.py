@@ -16,8 +16,10 @@ import subprocess
 import sys
 from collections import Counter
 
-path = sys.argv[1]
-kname = sys.argv[2] if len(sys.argv) > 2 else "k_linear_hash_rows"
+args = [a for a in sys.argv[1:] if not a.startswith("--chunk")]
+chunk = [int(a.split("=")[1]) for a in sys.argv[1:] if a.startswith("--chunk=")]
+path = args[0]
+kname = args[1] if len(args) > 1 else "k_linear_hash_rows"
 txt = subprocess.run(["cuobjdump", "-sass", path], capture_output=True, text=True).stdout
 cur, funcs = None, {}
 for line in txt.splitlines():
@@ -53,12 +55,31 @@ pre_wide = sum(1 for a, t in ins if pre[0] <= a <= pre[1] and "IMAD.WIDE" in t)
 pre_trips = 12 // max(1, round(pre_wide / 49.0))
 
 
+# rounds per trip of the partial-round loop (POS_PR_CHUNK): from --chunk=M, else from the loop's S-box squarings (2 per round)
+part_sq = sum(1 for a, t in ins if part[0] <= a <= part[1] and re.search(r"IMAD\.WIDE\.U32 R\d+, (R\d+)(\.reuse)?, \1(\.reuse)?, RZ", t))
+part_chunk = chunk[0] if chunk else max(1, round(part_sq / 4.0))      # x^2: a0*a0 and a1*a1 per squaring, two squarings per S-box
+# a second update loop behind the partial-round loop = a tail chunk (22 % M rounds); without one the rounds are padded at the front
+# to ceil(22 / M) trips (POS_PR_NOTAIL; the padded rounds skip their S-box and dot product: a slight over-count here)
+has_tail = len(nested) > 2
+part_trips = 22 // part_chunk if (has_tail or 22 % part_chunk == 0) else -(-22 // part_chunk)
+print("partial-round loop: %d round(s) per trip, %d trips%s" % (part_chunk, part_trips, " (+ %d in the tail)" % (22 % part_chunk) if has_tail else ""))
+
+
+# the rolled end-of-chunk update loops (11 trips, one per state word): every other loop of the round-3 branch -- the one inside the
+# partial-round loop and the one of the tail chunk
+upd = [l for l in nested[2:]] + [l for l in inner if part[0] < l[0] and l[1] < part[1]]
+print("update loops (11 trips each):", ["%#x-%#x" % l for l in upd])
+
+
 def weight(a):
+    for l in upd:
+        if l[0] <= a <= l[1]:
+            return 11 * (part_trips if part[0] <= a <= part[1] else 1)
     if pre[0] <= a <= pre[1]:
         return pre_trips
     if part[0] <= a <= part[1]:
-        return 22
-    if pre[1] < a < part[0]:
+        return part_trips
+    if pre[0] <= a <= full[1]:                 # the rest of the round-3 branch (laid out at the end of the loop body), incl. the tail chunk
         return 1
     if full[0] <= a <= full[1]:
         return 8

@@ -108,6 +108,29 @@ struct ProfScope {
     }
 };
 
+// Events of a multi-stream pipeline (streamed commit / Merkle tree / scatter).  Whatever way the function is left -- the CU()
+// and GLP() macros return early on an error -- the copy streams are drained before the events go away and before a later
+// ensure() may free the staging buffers they still have work queued on.
+struct PipelineEvents {
+    glp_ctx *ctx;
+    std::vector<cudaEvent_t> evs;
+    explicit PipelineEvents(glp_ctx *c) : ctx(c) {}
+    int make(cudaEvent_t *e, unsigned flags)
+    {
+        CU(cudaEventCreateWithFlags(e, flags));
+        evs.push_back(*e);
+        return GLP_OK;
+    }
+    ~PipelineEvents()
+    {
+        cudaStreamSynchronize(ctx->copy_stream[0]);
+        cudaStreamSynchronize(ctx->copy_stream[1]);
+        cudaStreamSynchronize(ctx->stream);
+        for (cudaEvent_t e : evs) cudaEventDestroy(e);
+        cudaGetLastError();
+    }
+};
+
 static int ensure(glp_ctx *ctx, DevBuf &b, size_t bytes)
 {
     if (b.bytes >= bytes) return GLP_OK;
@@ -941,12 +964,13 @@ extern "C" int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint
         GLP(ensure(ctx, ctx->work, (size_t)n_ext * w * sizeof(gl_t)));
         gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
         std::vector<cudaEvent_t> up(nblocks), used(nblocks);
+        PipelineEvents pe(ctx);
         for (uint64_t k = 0; k < nblocks; k++) {
-            CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
-            CU(cudaEventCreateWithFlags(&used[k], cudaEventDisableTiming));
+            GLP(pe.make(&up[k], cudaEventDisableTiming));
+            GLP(pe.make(&used[k], cudaEventDisableTiming));
         }
         cudaEvent_t start;
-        CU(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+        GLP(pe.make(&start, cudaEventDisableTiming));
         CU(cudaEventRecord(start, ctx->stream));
         CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
         auto width = [&](uint64_t k) { return (uint32_t)((ncols - k * w < w) ? ncols - k * w : w); };
@@ -966,10 +990,8 @@ extern "C" int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint
             CU(cudaEventRecord(used[k], ctx->stream));
             if (k + 2 < nblocks) GLP(upload(k + 2));
         }
-        cudaError_t e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->copy_stream[0]);
-        for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(used[k]); }
-        cudaEventDestroy(start);
-        CU(e0); CU(e1);
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaStreamSynchronize(ctx->copy_stream[0]));
         return GLP_OK;
     }
     // device input (which must not overlap any slab): optimistic passes, repeated exactly if they flag; returns synchronised
@@ -1142,12 +1164,13 @@ static int merkletree_streamed(glp_ctx *ctx, gl_t *dtree, const uint64_t *in, ui
     GLP(ensure(ctx, ctx->tmp_in, 2 * block_words * sizeof(gl_t)));
     gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + block_words};
     std::vector<cudaEvent_t> up(nblocks), hashed(nblocks);
+    PipelineEvents pe(ctx);
     for (uint64_t k = 0; k < nblocks; k++) {
-        CU(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&hashed[k], cudaEventDisableTiming));
+        GLP(pe.make(&up[k], cudaEventDisableTiming));
+        GLP(pe.make(&hashed[k], cudaEventDisableTiming));
     }
     cudaEvent_t start;
-    CU(cudaEventCreateWithFlags(&start, cudaEventDisableTiming));
+    GLP(pe.make(&start, cudaEventDisableTiming));
     CU(cudaEventRecord(start, ctx->stream));                                  // the staging buffers may still be in use by earlier work
     CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
     int rc = GLP_OK;
@@ -1166,10 +1189,7 @@ static int merkletree_streamed(glp_ctx *ctx, gl_t *dtree, const uint64_t *in, ui
         ProfScope ps(ctx, 3);
         rc = dev_tree_levels(ctx, dtree, nrows);
     }
-    cudaError_t e0 = cudaStreamSynchronize(ctx->copy_stream[0]);              // before the events go away
-    for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(hashed[k]); }
-    cudaEventDestroy(start);
-    CU(e0);
+    CU(cudaStreamSynchronize(ctx->copy_stream[0]));
     return rc;
 }
 
@@ -1391,18 +1411,23 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     col0[nblocks] = ncols;
     GLP(ensure(ctx, ctx->tmp_in, (full_stage ? (size_t)n * (col0[nblocks] + 8) : 2 * (size_t)n * w) * sizeof(gl_t)));
     if (!ext_dev) GLP(ensure(ctx, ctx->tmp_out, 2 * (size_t)n_ext * w * sizeof(gl_t)));
+    // the LDE scratch for the WIDEST block, before the streams fork: lde_block's own ensure() would otherwise free and
+    // reallocate it between the short first block and the next one -- cudaFree synchronises the whole device, uploads included
+    GLP(ensure(ctx, ctx->s2, (size_t)n * w * sizeof(gl_t)));
+    if (ctx->no_fused_lde) GLP(ensure(ctx, ctx->s1, (size_t)n_ext * w * sizeof(gl_t)));
     auto stage_of = [&](uint64_t k) { return (gl_t *)ctx->tmp_in.p + (full_stage ? (size_t)n * col0[k] : (k & 1) * (size_t)n * w); };
     gl_t *extb[2] = {(gl_t *)ctx->tmp_out.p, ext_dev ? nullptr : (gl_t *)ctx->tmp_out.p + (size_t)n_ext * w};
     std::vector<cudaEvent_t> up(nblocks), lde_done(nblocks), down(nblocks), hashed(nblocks);
     const unsigned evflags = ctx->trace ? cudaEventDefault : cudaEventDisableTiming;     // GLP_TRACE=1: print the pipeline's timeline
+    PipelineEvents pe(ctx);
     for (uint64_t k = 0; k < nblocks; k++) {
-        CU(cudaEventCreateWithFlags(&up[k], evflags));
-        CU(cudaEventCreateWithFlags(&lde_done[k], evflags));
-        CU(cudaEventCreateWithFlags(&down[k], evflags));
-        CU(cudaEventCreateWithFlags(&hashed[k], evflags));
+        GLP(pe.make(&up[k], evflags));
+        GLP(pe.make(&lde_done[k], evflags));
+        GLP(pe.make(&down[k], evflags));
+        GLP(pe.make(&hashed[k], evflags));
     }
     cudaEvent_t start;
-    CU(cudaEventCreateWithFlags(&start, evflags));
+    GLP(pe.make(&start, evflags));
     CU(cudaEventRecord(start, ctx->stream));                      // the copy streams must not run ahead of earlier work on the caller's stream
     CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
     CU(cudaStreamWaitEvent(ctx->copy_stream[1], start, 0));
@@ -1463,8 +1488,6 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         }
         cudaGetLastError();
     }
-    for (uint64_t k = 0; k < nblocks; k++) { cudaEventDestroy(up[k]); cudaEventDestroy(lde_done[k]); cudaEventDestroy(down[k]); cudaEventDestroy(hashed[k]); }
-    cudaEventDestroy(start);
     CU(e0); CU(e1); CU(e2);
     return GLP_OK;
 }
@@ -1657,6 +1680,10 @@ extern "C" int glp_const_tree(glp_ctx *ctx, uint64_t *const_tree, const uint64_t
     if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
     if (!const_tree || !const_pols) return fail(GLP_E_ARG, "glp_const_tree: NULL pointer");
     if (n == 0 || npols == 0) return fail(GLP_E_ARG, "glp_const_tree: empty input");
+    // everything glp_commit would reject, BEFORE the header is written: a failed call must not leave a plausible header in a
+    // buffer MerkleTreeGL(Element *) would parse
+    if (!is_pow2(n) || !is_pow2(n_ext) || n_ext < n) return fail(GLP_E_ARG, "glp_const_tree: sizes must be powers of two with n_ext >= n");
+    if (n_ext > (1ull << 32)) return fail(GLP_E_DOMAIN, "Domain size too big for the curve");
     CU(cudaSetDevice(ctx->device));
     const uint64_t header[2] = {npols, n_ext};
     CU(cudaMemcpyAsync(const_tree, header, sizeof header, cudaMemcpyDefault, ctx->stream));

@@ -81,6 +81,27 @@ GL_HD void gl_dot_mac(GlDotAcc &s, gl_t a, gl_t b)
 #endif
 }
 
+// acc += a * w for a 32-bit w: two of the four partial products (the chunked partial rounds' cross weights, POS_PR_CHUNK)
+GL_HD void gl_dot_mac_small(GlDotAcc &s, gl_t a, uint32_t w)
+{
+#if GL_DEVICE_PTX
+    asm("{\n\t"
+        ".reg .u32 a0,a1;\n\t"
+        "mov.b64 {a0,a1}, %6;\n\t"
+        "mad.lo.cc.u32 %0, a0, %7, %0;\n\t"
+        "madc.hi.cc.u32 %1, a0, %7, %1;\n\t"
+        "addc.u32 %2, %2, 0;\n\t"
+        "mad.lo.cc.u32 %3, a1, %7, %3;\n\t"
+        "madc.hi.cc.u32 %4, a1, %7, %4;\n\t"
+        "addc.u32 %5, %5, 0;\n\t"
+        "}"
+        : "+r"(s.z0), "+r"(s.z1), "+r"(s.zc), "+r"(s.x0), "+r"(s.x1), "+r"(s.xc)
+        : "l"(a), "r"(w));
+#else
+    gl_dot_mac(s, a, (gl_t)w);
+#endif
+}
+
 #ifndef POS_EPS_ALU_FOLD
 #define POS_EPS_ALU_FOLD 0
 #endif
@@ -520,8 +541,82 @@ GL_HD void pos_pre_layer(gl_t x[12], GlBorrow &bf)
 #endif
 }
 
+// ---- the partial rounds, M at a time ----
+// One round is  y = x0^7 + c;  s = 25 y + sum_{i>=1} x_i S_i;  x_i += y v_i (i >= 1);  x0 = s  (poseidon_goldilocks.cpp:19-32).  The
+// eleven rank-1 updates cost a full multiply AND a fold each.  Taken M rounds at a time they become one M-term dot product per
+// word with ONE fold (x_i + sum_k y_k v_i(k)), and the dot product of round k makes up for the updates it has not seen with
+// y_j * W_(k-j) for every earlier round j of the chunk -- where W_d = sum_i v_i(j) S_i(j+d) is the same for every j and SMALL
+// (13, 21, 29 bits for d = 1, 2, 3: two partial products instead of four), as is the diagonal weight 25; both facts are asserted
+// by tools/gen_poseidon_tables.py, which also checks this formulation against the plain one on the reference's known answers.
+// Per round: 22 + (M-1)/2 multiply-accumulates and 1 + 11/M folds instead of 12 multiply-accumulates, 11 multiplies and 12 folds.
+#ifndef POS_PR_NOTAIL
+#define POS_PR_NOTAIL 0           // 1 = pad at the front instead of a tail chunk: measured slower (the padded rounds' idle update loop costs
+#endif                            // more than the tail's 6 KB of code: 1135 against 1177 M perm/s, profiles/r02_pos_variants.txt)
+#ifndef POS_PR_CHUNK
+#define POS_PR_CHUNK 4            // 1 = round by round (round 1's kernel); M > 1: chunks of M, the remaining 22 % M rounds as one shorter chunk.
+                                  // Measured (M perm/s, 2^22 x 64): 1 1134, 2 1096, 3 1148, 4 1177, 5 1135, 6 1095, 7 1078 -- fewer
+                                  // instructions up to M = 6, but beyond 4 the hot loop (44 KB at M = 4) falls out of the instruction cache
+#endif
+GLP_CONSTANT gl_t POS_SPW[8] = {GLP_POSEIDON_SPW_INIT, 0};                 // W_d, d = 1..7; the first three fit 32 bits
+// Where state words 1..11 live during the partial rounds (POS_PR_CHUNK > 1): in the chunked form they are only read by the dot
+// products and rewritten once per chunk, so they sit in shared memory ([word][thread], conflict-free) and the end-of-chunk
+// update is a ROLLED loop over the word index -- one copy of its code instead of eleven (the hot loop stays inside the
+// instruction cache) and four carry predicates in flight instead of forty-four (with the update unrolled ptxas packs them into
+// a register bit mask: 220 LOP3 per chunk).  22 registers are free meanwhile.  The emulator hands in a thread-private array.
+struct PosXs {
+    gl_t *p;
+    uint32_t stride;
+};
+GL_HD gl_t &pos_xs_at(const PosXs &xs, int i) { return xs.p[(size_t)i * xs.stride]; }
+#if defined(GLP_EMU) || !defined(__CUDACC__)
+#define POS_XS_DECL(block) gl_t pos_xs_buf[11]; const PosXs xs = {pos_xs_buf, 1}
+#else
+#define POS_XS_DECL(block) __shared__ gl_t pos_xs_buf[11 * (block)]; const PosXs xs = {pos_xs_buf + threadIdx.x, (uint32_t)(block)}
+#endif
+// Rounds p .. p+M-1; rounds with a negative index do nothing (POS_PR_NOTAIL: the 22 rounds are padded at the FRONT to a whole
+// number of chunks instead of a second, shorter copy of this code behind the loop -- the hot loop has to fit the instruction
+// cache, and 6 KB of tail pushed M = 4 to its edge; the price is 11 * 6 idle multiply-accumulate instructions per padded round).
+template <bool DEFER, int M>
+GL_HD void pos_partial_chunk(gl_t &x0, const PosXs &xs, const int p, GlBorrow &bf)
+{
+    static_assert(M >= 1 && M <= 8, "cross weights W_d are tabulated for d <= 7");
+    gl_t y[M];
+#pragma unroll
+    for (int k = 0; k < M; k++) {
+        y[k] = 0;
+        if (p + k >= 0) {                                         // uniform; false only for the padding rounds of the first chunk
+            const gl_t *S = POS_SP + 23 * (p + k);
+            y[k] = gl_add_c(pos_pow7<DEFER>(x0, bf), POS_RC[60 + p + k]);
+            GlDotAcc acc;
+            gl_dot_init(acc);
+            gl_dot_mac_small(acc, y[k], GLP_POSEIDON_SP_DIAG);
+#pragma unroll
+            for (int i = 1; i < 12; i++) gl_dot_mac(acc, pos_xs_at(xs, i - 1), S[i]);
+#pragma unroll
+            for (int j = 0; j < k; j++) {
+                if (k - j <= 3) gl_dot_mac_small(acc, y[j], (uint32_t)POS_SPW[k - j - 1]);
+                else gl_dot_mac(acc, y[j], POS_SPW[k - j - 1]);
+            }
+            x0 = gl_dot_fold<DEFER>(acc, bf);
+        }
+    }
+    const gl_t *S0 = POS_SP + 23 * (p < 0 ? 0 : p);              // padded rounds multiply y = 0 by whatever round 0's weights are
+    const int koff = p < 0 ? p : 0;
+#pragma unroll 1
+    for (int i = 1; i < 12; i++) {
+        GlDotAcc acc;
+        gl_dot_init(acc);
+        const gl_t xi = pos_xs_at(xs, i - 1);
+        acc.z0 = (uint32_t)xi;
+        acc.z1 = (uint32_t)(xi >> 32);
+#pragma unroll
+        for (int k = 0; k < M; k++) gl_dot_mac(acc, y[k], S0[23 * (k + koff < 0 ? 0 : k + koff) + 11 + i]);
+        pos_xs_at(xs, i - 1) = gl_dot_fold<DEFER>(acc, bf);
+    }
+}
+
 template <bool LOCKSTEP, bool DEFER>
-GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf)
+GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf, const PosXs &xs)
 {
 #pragma unroll
     for (int i = 0; i < 12; i++) x[i] = gl_add_c(x[i], POS_RC[i]);
@@ -548,6 +643,29 @@ GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf)
 #endif
             pos_pre_layer<DEFER>(x, bf);
             // partial rounds: x0 = x0^7 + C;  s0 = <x, S[0..12)>;  x_i += x0 * S[11+i] (i >= 1);  x0 = s0
+#if POS_PR_CHUNK > 1
+            {
+                constexpr int M = POS_PR_CHUNK, TAIL = 22 % POS_PR_CHUNK;
+#pragma unroll
+                for (int i = 1; i < 12; i++) pos_xs_at(xs, i - 1) = x[i];
+#if POS_PR_NOTAIL
+#pragma unroll 1
+                for (int p = TAIL ? TAIL - M : 0; p < 22; p += M) {
+                    pos_round_sync<LOCKSTEP>();
+                    pos_partial_chunk<DEFER, M>(x[0], xs, p, bf);
+                }
+#else
+#pragma unroll 1
+                for (int p = 0; p + M <= 22; p += M) {
+                    pos_round_sync<LOCKSTEP>();
+                    pos_partial_chunk<DEFER, M>(x[0], xs, p, bf);
+                }
+                if (TAIL) pos_partial_chunk<DEFER, (TAIL ? TAIL : 1)>(x[0], xs, 22 - TAIL, bf);
+#endif
+#pragma unroll
+                for (int i = 1; i < 12; i++) x[i] = pos_xs_at(xs, i - 1);
+            }
+#else
 #pragma unroll 1
             for (int p = 0; p < 22; p++) {
                 pos_round_sync<LOCKSTEP>();
@@ -567,12 +685,13 @@ GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf)
                 }
                 x[0] = gl_dot_fold<DEFER>(acc, bf);
             }
+#endif
         }
     }
 }
 
-GL_HD void pos_permute(gl_t x[12])
+GL_HD void pos_permute(gl_t x[12], const PosXs &xs)
 {
     GlBorrow bf = gl_borrow_init();
-    pos_permute_t<false, false>(x, bf);
+    pos_permute_t<false, false>(x, bf, xs);
 }

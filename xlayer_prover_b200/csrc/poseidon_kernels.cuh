@@ -74,7 +74,7 @@ static unsigned long long g_pos_redo_rows;                       // the emulator
 
 // the sponge over one row; returns whether a deferred wrap fired (never when !DEFER)
 template <bool LOCKSTEP, bool DEFER>
-static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap)
+static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap, const PosXs &xs)
 {
     gl_t nxt[8];
     GlBorrow bf = gl_borrow_init();
@@ -90,16 +90,16 @@ static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__re
             uint64_t rem = ncols - 8 * (b + 1);
             pos_load8(nxt, p + 8 * (b + 1), (uint32_t)(rem < 8 ? rem : 8), vec16);
         }
-        pos_permute_t<LOCKSTEP, DEFER>(x, bf);
+        pos_permute_t<LOCKSTEP, DEFER>(x, bf, xs);
 #pragma unroll
         for (int i = 0; i < 4; i++) x[8 + i] = x[i];   // next capacity = first 4 outputs (:247-250)
     }
     return DEFER && gl_borrow_hit(bf);
 }
-static __device__ GLP_NOINLINE void pos_leaf_row_exact(gl_t *o, const gl_t *p, uint64_t ncols, int vec16, const gl_t *cap)
+static __device__ GLP_NOINLINE void pos_leaf_row_exact(gl_t *o, const gl_t *p, uint64_t ncols, int vec16, const gl_t *cap, PosXs xs)
 {
     gl_t x[12];
-    pos_leaf_row<false, false>(x, p, ncols, vec16 != 0, cap);
+    pos_leaf_row<false, false>(x, p, ncols, vec16 != 0, cap, xs);
 #pragma unroll
     for (int i = 0; i < 4; i++) o[i] = gl_canon(x[i]);
     POS_COUNT_REDO();
@@ -110,6 +110,7 @@ __global__ void POS_LEAF_BOUNDS
 k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint64_t pitch, uint64_t nrows, int vec16, const gl_t *cap_in,
                    uint64_t out_pitch)
 {
+    POS_XS_DECL(POS_LEAF_BLOCK);
     constexpr bool DEFER = POS_DEFER_BORROW && !LOCKSTEP;     // a redone row would miss the other warps' barriers
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = row < nrows;
@@ -128,9 +129,9 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     }
     const gl_t *cap = cap_in ? cap_in + row * out_pitch : nullptr;
     gl_t x[12];
-    const bool bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap);
+    const bool bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap, xs);
     if (DEFER && bf) {                            // before any store: cap_in may alias out
-        pos_leaf_row_exact(o, p, ncols, vec16, cap);
+        pos_leaf_row_exact(o, p, ncols, vec16, cap, xs);
         return;
     }
     if (live) {
@@ -140,19 +141,19 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
 }
 
 // parents[i] = H(children[2i] || children[2i+1] || 0000)[0:4]; the same deferred wrap and exact redo as the leaf rows
-static __device__ GLP_NOINLINE void pos_hash_pair_exact(gl_t *dst, const gl_t *src)
+static __device__ GLP_NOINLINE void pos_hash_pair_exact(gl_t *dst, const gl_t *src, PosXs xs)
 {
     gl_t x[12];
 #pragma unroll
     for (int i = 0; i < 8; i++) x[i] = src[i];
 #pragma unroll
     for (int i = 8; i < 12; i++) x[i] = 0;
-    pos_permute(x);
+    pos_permute(x, xs);
 #pragma unroll
     for (int i = 0; i < 4; i++) dst[i] = gl_canon(x[i]);
     POS_COUNT_REDO();
 }
-static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src)
+static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, const gl_t *__restrict__ src, const PosXs &xs)
 {
     gl_t x[12];
 #pragma unroll
@@ -160,9 +161,9 @@ static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, con
 #pragma unroll
     for (int i = 8; i < 12; i++) x[i] = 0;
     GlBorrow bf = gl_borrow_init();
-    pos_permute_t<false, POS_DEFER_BORROW != 0>(x, bf);
+    pos_permute_t<false, POS_DEFER_BORROW != 0>(x, bf, xs);
     if (POS_DEFER_BORROW && gl_borrow_hit(bf)) {
-        pos_hash_pair_exact(dst, src);
+        pos_hash_pair_exact(dst, src, xs);
         return;
     }
 #pragma unroll
@@ -172,9 +173,10 @@ static __device__ __forceinline__ void pos_hash_pair(gl_t *__restrict__ dst, con
 __global__ void __launch_bounds__(POS_BLOCK)
 k_tree_level(gl_t *__restrict__ parents, const gl_t *__restrict__ children, uint64_t nparents)
 {
+    POS_XS_DECL(POS_BLOCK);
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nparents) return;
-    pos_hash_pair(parents + 4 * i, children + 8 * i);
+    pos_hash_pair(parents + 4 * i, children + 8 * i, xs);
 }
 
 // One CTA walks the remaining levels: `level` holds n nodes (n a power of two, n <= 2*blockDim.x) followed
@@ -183,11 +185,12 @@ k_tree_level(gl_t *__restrict__ parents, const gl_t *__restrict__ children, uint
 __global__ void __launch_bounds__(POS_TOP_THREADS)
 k_tree_top(gl_t *level, uint64_t n)
 {
+    POS_XS_DECL(POS_TOP_THREADS);
     gl_t *cur = level;
     while (n > 1) {
         uint64_t np = n >> 1;
         gl_t *par = cur + 4 * n;
-        if (threadIdx.x < np) pos_hash_pair(par + 4 * threadIdx.x, cur + 8 * threadIdx.x);
+        if (threadIdx.x < np) pos_hash_pair(par + 4 * threadIdx.x, cur + 8 * threadIdx.x, xs);
         __syncthreads();
         cur = par;
         n = np;
@@ -197,12 +200,13 @@ k_tree_top(gl_t *level, uint64_t n)
 __global__ void __launch_bounds__(POS_BLOCK)
 k_permute_batch(gl_t *__restrict__ out, const gl_t *__restrict__ in, uint64_t n)
 {
+    POS_XS_DECL(POS_BLOCK);
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     gl_t x[12];
 #pragma unroll
     for (int k = 0; k < 12; k++) x[k] = in[12 * i + k];
-    pos_permute(x);
+    pos_permute(x, xs);
 #pragma unroll
     for (int k = 0; k < 12; k++) out[12 * i + k] = gl_canon(x[k]);
 }
