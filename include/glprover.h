@@ -150,7 +150,7 @@ int glp_merkle_group_proofs(glp_ctx *ctx, uint64_t *proofs, const uint64_t *sour
 /* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
  * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip
  * in between.  out_ext and tree may be NULL when the caller only needs the root (they are then kept in
- * device scratch).  With a host `in` the commit is a pipeline over column blocks (GLP_STREAM_COLS columns, default 96):
+ * device scratch).  With a host `in` the commit is a pipeline over column blocks (GLP_STREAM_COLS columns, default 160):
  * upload of block k+1, LDE + sponge absorption of block k and download of block k-1 overlap on three streams. */
 int glp_commit(glp_ctx *ctx, uint64_t *out_ext, uint64_t *tree, uint64_t root[4], const uint64_t *in,
                uint64_t n, uint64_t n_ext, uint64_t ncols);

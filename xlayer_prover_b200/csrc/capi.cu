@@ -47,7 +47,8 @@ struct TwoLevel {
 struct glp_ctx {
     int device = 0;
     cudaStream_t own_stream = nullptr, stream = nullptr;
-    cudaStream_t copy_stream[2] = {nullptr, nullptr};
+    cudaStream_t copy_stream[3] = {nullptr, nullptr, nullptr};   // [0] uploads, [1] downloads, [2] second download stream (GLP_D2H_SPLIT)
+    uint32_t d2h_split = 2;                  // the streamed commit downloads each column block as this many row ranges on separate streams
     cudaStream_t lde_stream = nullptr;       // high priority: the LDE of column block k+1 under the leaf hash of block k (commit_overlapped)
     // co-resident NTT passes (k_ntt_pass_co): > 0 while the launches of an LDE should use the small resident grid
     uint32_t co_active = 0;
@@ -57,7 +58,7 @@ struct glp_ctx {
     int sm_count = 148;
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
-    uint64_t stream_cols = 96;               // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
+    uint64_t stream_cols = 160;              // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
@@ -125,6 +126,7 @@ struct PipelineEvents {
     {
         cudaStreamSynchronize(ctx->copy_stream[0]);
         cudaStreamSynchronize(ctx->copy_stream[1]);
+        cudaStreamSynchronize(ctx->copy_stream[2]);
         cudaStreamSynchronize(ctx->stream);
         for (cudaEvent_t e : evs) cudaEventDestroy(e);
         cudaGetLastError();
@@ -184,6 +186,7 @@ extern "C" int glp_init(int device, glp_ctx **out)
     CU(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[0], cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&ctx->copy_stream[1], cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&ctx->copy_stream[2], cudaStreamNonBlocking));
     ctx->stream = ctx->own_stream;
     {
         int lo = 0, hi = 0;
@@ -217,6 +220,8 @@ extern "C" int glp_init(int device, glp_ctx **out)
     if (msm && atoll(msm) > 0) ctx->merkle_stream_min = (uint64_t)atoll(msm);
     const char *sa = getenv("GLP_STAGE_ALL");
     if (sa) ctx->stage_all = atoi(sa) != 0;
+    const char *ds = getenv("GLP_D2H_SPLIT");
+    if (ds && atoi(ds) >= 1 && atoi(ds) <= 2) ctx->d2h_split = (uint32_t)atoi(ds);
     const char *sc = getenv("GLP_STREAM_COLS");
     if (sc && atoi(sc) >= 8) ctx->stream_cols = (uint64_t)(atoi(sc) / 8) * 8;
     *out = ctx;
@@ -236,6 +241,7 @@ extern "C" void glp_destroy(glp_ctx *ctx)
     cudaStreamDestroy(ctx->own_stream);
     cudaStreamDestroy(ctx->copy_stream[0]);
     cudaStreamDestroy(ctx->copy_stream[1]);
+    cudaStreamDestroy(ctx->copy_stream[2]);
     cudaStreamDestroy(ctx->lde_stream);
     delete ctx;
 }
@@ -1371,7 +1377,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     const bool want_ext = out_ext != nullptr;
     const size_t tree_words = glp_tree_num_elements(n_ext);
     const uint32_t logN = ilog2_u64(n), logE = ilog2_u64(n_ext);
-    // block width: GLP_STREAM_COLS (default 96), shrunk to fit the scratch budget
+    // block width: GLP_STREAM_COLS (default 160), shrunk to fit the scratch budget
     uint64_t w = ctx->stream_cols;
     bool full_stage = false;
     {
@@ -1417,7 +1423,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     if (ctx->no_fused_lde) GLP(ensure(ctx, ctx->s1, (size_t)n_ext * w * sizeof(gl_t)));
     auto stage_of = [&](uint64_t k) { return (gl_t *)ctx->tmp_in.p + (full_stage ? (size_t)n * col0[k] : (k & 1) * (size_t)n * w); };
     gl_t *extb[2] = {(gl_t *)ctx->tmp_out.p, ext_dev ? nullptr : (gl_t *)ctx->tmp_out.p + (size_t)n_ext * w};
-    std::vector<cudaEvent_t> up(nblocks), lde_done(nblocks), down(nblocks), hashed(nblocks);
+    std::vector<cudaEvent_t> up(nblocks), lde_done(nblocks), down(nblocks), hashed(nblocks), half(nblocks);
     const unsigned evflags = ctx->trace ? cudaEventDefault : cudaEventDisableTiming;     // GLP_TRACE=1: print the pipeline's timeline
     PipelineEvents pe(ctx);
     for (uint64_t k = 0; k < nblocks; k++) {
@@ -1425,12 +1431,14 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         GLP(pe.make(&lde_done[k], evflags));
         GLP(pe.make(&down[k], evflags));
         GLP(pe.make(&hashed[k], evflags));
+        GLP(pe.make(&half[k], cudaEventDisableTiming));
     }
     cudaEvent_t start;
     GLP(pe.make(&start, evflags));
     CU(cudaEventRecord(start, ctx->stream));                      // the copy streams must not run ahead of earlier work on the caller's stream
     CU(cudaStreamWaitEvent(ctx->copy_stream[0], start, 0));
     CU(cudaStreamWaitEvent(ctx->copy_stream[1], start, 0));
+    CU(cudaStreamWaitEvent(ctx->copy_stream[2], start, 0));
     auto width = [&](uint64_t k) { return (uint32_t)(col0[k + 1] - col0[k]); };
     auto upload = [&](uint64_t k) -> int {
         if (k >= 2 && !full_stage) CU(cudaStreamWaitEvent(ctx->copy_stream[0], lde_done[k - 2], 0));   // staging buffer read by block k-2's INTT
@@ -1454,9 +1462,19 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         CU(cudaEventRecord(lde_done[k], ctx->stream));
         if (k + 2 < nblocks && !full_stage) GLP(upload(k + 2));
         if (want_ext && !ext_dev) {
+            // one strided 2-D copy keeps a single copy engine busy at 45-49 GB/s; two halves of the rows on two streams run on
+            // two engines (GLP_D2H_SPLIT, profiles/r02_e2e_trace.txt)
+            const uint64_t r1 = (ctx->d2h_split == 2 && n_ext >= 4096) ? n_ext / 2 : n_ext;
             CU(cudaStreamWaitEvent(ctx->copy_stream[1], lde_done[k], 0));
-            CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)out_pitch * 8, eb, (size_t)wk * 8, (size_t)wk * 8, n_ext, cudaMemcpyDeviceToHost,
+            CU(cudaMemcpy2DAsync(out_ext + c0, (size_t)out_pitch * 8, eb, (size_t)wk * 8, (size_t)wk * 8, r1, cudaMemcpyDeviceToHost,
                                  ctx->copy_stream[1]));
+            if (r1 < n_ext) {
+                CU(cudaStreamWaitEvent(ctx->copy_stream[2], lde_done[k], 0));
+                CU(cudaMemcpy2DAsync(out_ext + r1 * out_pitch + c0, (size_t)out_pitch * 8, eb + r1 * eb_pitch, (size_t)wk * 8, (size_t)wk * 8,
+                                     n_ext - r1, cudaMemcpyDeviceToHost, ctx->copy_stream[2]));
+                CU(cudaEventRecord(half[k], ctx->copy_stream[2]));
+                CU(cudaStreamWaitEvent(ctx->copy_stream[1], half[k], 0));   // down[k] = both halves
+            }
             CU(cudaEventRecord(down[k], ctx->copy_stream[1]));
         }
         if (want_tree) {
