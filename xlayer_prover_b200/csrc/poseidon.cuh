@@ -553,10 +553,13 @@ GL_HD void pos_pre_layer(gl_t x[12], GlBorrow &bf)
 #define POS_PR_NOTAIL 0           // 1 = pad at the front instead of a tail chunk: measured slower (the padded rounds' idle update loop costs
 #endif                            // more than the tail's 6 KB of code: 1135 against 1177 M perm/s, profiles/r02_pos_variants.txt)
 #ifndef POS_PR_CHUNK
-#define POS_PR_CHUNK 4            // 1 = round by round (round 1's kernel); M > 1: chunks of M, the remaining 22 % M rounds as one shorter chunk.
-                                  // Measured (M perm/s, 2^22 x 64): 1 1134, 2 1096, 3 1148, 4 1177, 5 1135, 6 1095, 7 1078 -- fewer
-                                  // instructions up to M = 6, but beyond 4 the hot loop (44 KB at M = 4) falls out of the instruction cache
-#endif
+#define POS_PR_CHUNK 1            // 1 = round by round (the default); M > 1: chunks of M rounds, the remaining 22 % M as one shorter chunk.
+#endif                            // Measured (M perm/s, profiles/r02_pos_variants.txt).  Rows of 64 columns (8 permutations a row, the warps of
+                                  // an SM start together and stay in phase): M = 1 1134, 2 1096, 3 1148, 4 1177, 5 1135, 6 1095.  Rows of 660
+                                  // columns (83 permutations a row: steady state, 16 warps spread over the whole 44 KB loop): M = 1 1135, 3 1141,
+                                  // 4 1061 (1144 with 3 CTAs of 166 registers).  The 4 % that fewer instructions buy exist only while the warps
+                                  // share their instruction and constant fetches; at the width the commit runs at they are gone, so the plain
+                                  // form stays the default and this one is kept as a measured alternative (bit-identical: emulator + GPU tests).
 GLP_CONSTANT gl_t POS_SPW[8] = {GLP_POSEIDON_SPW_INIT, 0};                 // W_d, d = 1..7; the first three fit 32 bits
 // Where state words 1..11 live during the partial rounds (POS_PR_CHUNK > 1): in the chunked form they are only read by the dot
 // products and rewritten once per chunk, so they sit in shared memory ([word][thread], conflict-free) and the end-of-chunk
@@ -577,14 +580,14 @@ GL_HD gl_t &pos_xs_at(const PosXs &xs, int i) { return xs.p[(size_t)i * xs.strid
 // number of chunks instead of a second, shorter copy of this code behind the loop -- the hot loop has to fit the instruction
 // cache, and 6 KB of tail pushed M = 4 to its edge; the price is 11 * 6 idle multiply-accumulate instructions per padded round).
 template <bool DEFER, int M>
-GL_HD void pos_partial_chunk(gl_t &x0, const PosXs &xs, const int p, GlBorrow &bf)
+GL_HD void pos_partial_chunk(gl_t &x0, const PosXs &xs, const int p, GlBorrow &bf, const int m = M)
 {
     static_assert(M >= 1 && M <= 8, "cross weights W_d are tabulated for d <= 7");
     gl_t y[M];
 #pragma unroll
     for (int k = 0; k < M; k++) {
         y[k] = 0;
-        if (p + k >= 0) {                                         // uniform; false only for the padding rounds of the first chunk
+        if (p + k >= 0 && k < m) {                                // uniform; false only for padding rounds (POS_PR_NOTAIL 1: front, 2: back)
             const gl_t *S = POS_SP + 23 * (p + k);
             y[k] = gl_add_c(pos_pow7<DEFER>(x0, bf), POS_RC[60 + p + k]);
             GlDotAcc acc;
@@ -610,7 +613,8 @@ GL_HD void pos_partial_chunk(gl_t &x0, const PosXs &xs, const int p, GlBorrow &b
         acc.z0 = (uint32_t)xi;
         acc.z1 = (uint32_t)(xi >> 32);
 #pragma unroll
-        for (int k = 0; k < M; k++) gl_dot_mac(acc, y[k], S0[23 * (k + koff < 0 ? 0 : k + koff) + 11 + i]);
+        for (int k = 0; k < M; k++)
+            if (k < m) gl_dot_mac(acc, y[k], S0[23 * (k + koff < 0 ? 0 : k + koff) + 11 + i]);   // uniform branch; k >= m only in a short last chunk
         pos_xs_at(xs, i - 1) = gl_dot_fold<DEFER>(acc, bf);
     }
 }
@@ -648,7 +652,13 @@ GL_HD void pos_permute_t(gl_t x[12], GlBorrow &bf, const PosXs &xs)
                 constexpr int M = POS_PR_CHUNK, TAIL = 22 % POS_PR_CHUNK;
 #pragma unroll
                 for (int i = 1; i < 12; i++) pos_xs_at(xs, i - 1) = x[i];
-#if POS_PR_NOTAIL
+#if POS_PR_NOTAIL == 2
+#pragma unroll 1
+                for (int p = 0; p < 22; p += M) {                  // the last chunk runs the same code with 22 - p < M active rounds
+                    pos_round_sync<LOCKSTEP>();
+                    pos_partial_chunk<DEFER, M>(x[0], xs, p, bf, 22 - p < M ? 22 - p : M);
+                }
+#elif POS_PR_NOTAIL
 #pragma unroll 1
                 for (int p = TAIL ? TAIL - M : 0; p < 22; p += M) {
                     pos_round_sync<LOCKSTEP>();
