@@ -545,6 +545,8 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
             if hext_p:
                 ctx.host_free(hext_p)
                 hext_p = None
+            ctx.release_scratch()                                   # the host-pointer leg's staging buffers (~100 GB) would not fit next to dext
+            torch.cuda.empty_cache()
             dext = torch.empty(n_ext * C, dtype=torch.int64, device=dev)
             dtree = torch.empty(tree_num_elements(n_ext), dtype=torch.int64, device=dev)
             nq = 128
@@ -569,6 +571,7 @@ def run_e2e(args, ctx, torch, dist, dev, stream, sc, rank, world, n, n_ext, C, c
                         "root_equals_host_path": [int(x) for x in np.asarray(rroot).view(np.uint64)] == [int(x) for x in np.asarray(root).view(np.uint64)],
                         "note": "H2D trace; extension and tree stay in HBM; D2H root + 128 query proofs (one glp_merkle_group_proofs call)"}
             del dext, dtree
+            torch.cuda.empty_cache()
         except Exception as ex:
             resident = {"value": None, "note": "failed: %r" % (ex,)}
     for p in (hin_p, hext_p, htree_p):

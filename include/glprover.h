@@ -55,6 +55,9 @@ uint64_t glp_ntt_retry_count(const glp_ctx *ctx);
 /* cap on internal scratch in bytes (0 = default: a quarter of free device memory, at most 16 GiB) */
 int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes);
 
+/* frees the context's internal device buffers (staging, scratch, private result copies); they come back on demand */
+int glp_release_scratch(glp_ctx *ctx);
+
 /* ---- memory helpers (for callers that keep data resident on the device) ---- */
 int glp_device_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr);
 int glp_device_free(glp_ctx *ctx, void *ptr);

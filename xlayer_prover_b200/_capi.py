@@ -29,6 +29,7 @@ SIGNATURES = {
     "glp_leaf_redo_rows": (u64, [vp]),
     "glp_ntt_retry_count": (u64, [vp]),
     "glp_set_scratch_limit": (i32, [vp, u64]),
+    "glp_release_scratch": (i32, [vp]),
     "glp_device_alloc": (i32, [vp, u64, C.POINTER(vp)]),
     "glp_device_free": (i32, [vp, vp]),
     "glp_host_alloc": (i32, [vp, u64, C.POINTER(vp)]),
@@ -165,6 +166,8 @@ class Context:
     def leaf_redo_rows(self): return int(self.lib.glp_leaf_redo_rows(self.h))
     def ntt_retry_count(self): return int(self.lib.glp_ntt_retry_count(self.h))
     def set_scratch_limit(self, nbytes): self.lib.check(self.lib.glp_set_scratch_limit(self.h, nbytes))
+
+    def release_scratch(self): self.lib.check(self.lib.glp_release_scratch(self.h))
 
     def device_alloc(self, nbytes):
         p = vp()

@@ -279,6 +279,22 @@ extern "C" int glp_set_scratch_limit(glp_ctx *ctx, uint64_t bytes)
     return GLP_OK;
 }
 
+// hand the context's internal device buffers (staging, NTT scratch, private copies of results) back to the driver; they are
+// allocated again on demand.  For callers that alternate between the host-pointer and the device-resident entry points
+// at sizes where both sets of buffers do not fit next to each other (bench.py's e2e legs at 2^23 x 660).
+extern "C" int glp_release_scratch(glp_ctx *ctx)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    CU(cudaSetDevice(ctx->device));
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->copy_stream[0]));
+    CU(cudaStreamSynchronize(ctx->copy_stream[1]));
+    CU(cudaStreamSynchronize(ctx->copy_stream[2]));
+    release(ctx->s1); release(ctx->s2); release(ctx->ext); release(ctx->nodes);
+    release(ctx->tmp_in); release(ctx->tmp_out); release(ctx->work);
+    return GLP_OK;
+}
+
 extern "C" int glp_device_alloc(glp_ctx *ctx, uint64_t bytes, void **ptr)
 {
     if (!ctx || !ptr) return fail(GLP_E_ARG, "glp_device_alloc: NULL argument");
