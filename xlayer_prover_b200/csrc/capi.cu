@@ -981,7 +981,10 @@ extern "C" int glp_extend_pol_scatter(glp_ctx *ctx, uint64_t *const *parts, uint
         // host input: upload column block k+1 (strided 2-D copy) while block k is extended and scattered
         uint64_t w = ctx->stream_cols;
         if (w > ncols) w = ncols;
-        const uint64_t nblocks = (ncols + w - 1) / w;
+        uint64_t nblocks = (ncols + w - 1) / w;
+        if (nblocks == 1 && ncols >= 64) nblocks = 2;              // something to overlap the first upload with
+        w = ((ncols + nblocks - 1) / nblocks + 7) / 8 * 8;         // equal blocks (a 165-column slice is 88 + 77, not 160 + 5)
+        nblocks = (ncols + w - 1) / w;
         GLP(ensure(ctx, ctx->tmp_in, 2 * (size_t)n * w * sizeof(gl_t)));
         GLP(ensure(ctx, ctx->work, (size_t)n_ext * w * sizeof(gl_t)));
         gl_t *stage[2] = {(gl_t *)ctx->tmp_in.p, (gl_t *)ctx->tmp_in.p + (size_t)n * w};
