@@ -49,7 +49,7 @@ POS_ALG_DFMA = 7 * 2 * 144
 #     instructions per permutation by pipe; costs measured in round 1 (profiles/r01_int_pipes.txt): IMAD.WIDE 4 cycles of the
 #     fmaheavy pipe per warp instruction per SM sub-partition, other IMAD, DFMA/I2F and every ALU op 2.  `roofline_sass` is
 #     the multiplier-pipe bound of that stream (how close the kernel runs to its own SASS, not to the algorithm).
-POS_SASS = {"instructions": 18543, "imad_wide": 5096, "imad_other": 948, "fp64": 2304, "alu": 8838}
+POS_SASS = {"instructions": 17409, "imad_wide": 4955, "imad_other": 1040, "fp64": 2304, "alu": 7628}
 POS_PIPE_CYCLES = {"fmaheavy": 4 * POS_SASS["imad_wide"] + 2 * POS_SASS["imad_other"], "fp64": 2 * POS_SASS["fp64"],
                    "alu": 2 * POS_SASS["alu"], "issue": POS_SASS["instructions"]}
 POS_BOUND_CYCLES = POS_PIPE_CYCLES["fmaheavy"] + POS_PIPE_CYCLES["fp64"]

@@ -553,13 +553,12 @@ GL_HD void pos_pre_layer(gl_t x[12], GlBorrow &bf)
 #define POS_PR_NOTAIL 0           // 1 = pad at the front instead of a tail chunk: measured slower (the padded rounds' idle update loop costs
 #endif                            // more than the tail's 6 KB of code: 1135 against 1177 M perm/s, profiles/r02_pos_variants.txt)
 #ifndef POS_PR_CHUNK
-#define POS_PR_CHUNK 1            // 1 = round by round (the default); M > 1: chunks of M rounds, the remaining 22 % M as one shorter chunk.
-#endif                            // Measured (M perm/s, profiles/r02_pos_variants.txt).  Rows of 64 columns (8 permutations a row, the warps of
-                                  // an SM start together and stay in phase): M = 1 1134, 2 1096, 3 1148, 4 1177, 5 1135, 6 1095.  Rows of 660
-                                  // columns (83 permutations a row: steady state, 16 warps spread over the whole 44 KB loop): M = 1 1135, 3 1141,
-                                  // 4 1061 (1144 with 3 CTAs of 166 registers).  The 4 % that fewer instructions buy exist only while the warps
-                                  // share their instruction and constant fetches; at the width the commit runs at they are gone, so the plain
-                                  // form stays the default and this one is kept as a measured alternative (bit-identical: emulator + GPU tests).
+#define POS_PR_CHUNK 5            // 1 = round by round (round 1's form); M > 1: chunks of M rounds, the remaining 22 % M as one shorter chunk.
+#endif                            // Measured (M perm/s, profiles/r02_pos_variants.txt).  The chunked forms need the warps of a CTA IN PHASE: they are
+                                  // 40-55 KB of hot code, and on long rows (660 columns = 83 permutations) free-running warps spread over the whole
+                                  // loop and stop sharing instruction and constant fetches -- M = 4 falls from 1177 (64-column rows, where a CTA's
+                                  // warps start together) to 1061, below M = 1's 1135.  With one __syncthreads() per permutation in the leaf kernel
+                                  // (POS_LEAF_SYNC, poseidon_kernels.cuh) they are width-independent: M = 1 1136, 3 1143, 4 1176, 5 1186, 6 1182-1193.
 GLP_CONSTANT gl_t POS_SPW[8] = {GLP_POSEIDON_SPW_INIT, 0};                 // W_d, d = 1..7; the first three fit 32 bits
 // Where state words 1..11 live during the partial rounds (POS_PR_CHUNK > 1): in the chunked form they are only read by the dot
 // products and rewritten once per chunk, so they sit in shared memory ([word][thread], conflict-free) and the end-of-chunk

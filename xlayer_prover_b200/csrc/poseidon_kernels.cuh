@@ -73,7 +73,12 @@ static unsigned long long g_pos_redo_rows;                       // the emulator
 #endif
 
 // the sponge over one row; returns whether a deferred wrap fired (never when !DEFER)
-template <bool LOCKSTEP, bool DEFER>
+#ifndef POS_LEAF_SYNC
+#define POS_LEAF_SYNC 1             // the warps of a CTA meet at a barrier before every permutation of the sponge: on long rows they would drift apart and
+                                    // stop sharing instruction / constant fetches (see POS_PR_CHUNK).  Rows past the end are clamped, not skipped; the exact
+                                    // redo of a flagged row runs after the loop and has no barrier in it
+#endif
+template <bool LOCKSTEP, bool DEFER, bool SYNC = false>
 static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__restrict__ p, uint64_t ncols, bool vec16, const gl_t *cap, const PosXs &xs)
 {
     gl_t nxt[8];
@@ -84,6 +89,9 @@ static __device__ __forceinline__ bool pos_leaf_row(gl_t x[12], const gl_t *__re
     for (int i = 8; i < 12; i++) x[i] = cap ? cap[i - 8] : 0;   // capacity starts at zero (:243-246)
 #pragma unroll 1
     for (uint64_t b = 0; b < nblk; b++) {
+#if !defined(GLP_EMU)
+        if (SYNC) __syncthreads();
+#endif
 #pragma unroll
         for (int i = 0; i < 8; i++) x[i] = nxt[i];
         if (b + 1 < nblk) {                        // prefetch the next 64 bytes of this row under the permutation
@@ -114,8 +122,9 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     constexpr bool DEFER = POS_DEFER_BORROW && !LOCKSTEP;     // a redone row would miss the other warps' barriers
     uint64_t row = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = row < nrows;
+    constexpr bool SYNC = POS_LEAF_SYNC != 0 && !LOCKSTEP;
     if (!live) {
-        if (!LOCKSTEP) return;
+        if (!LOCKSTEP && !SYNC) return;
         row = nrows - 1;
     }
     const gl_t *p = in + row * pitch;
@@ -129,9 +138,9 @@ k_linear_hash_rows(gl_t *out, const gl_t *__restrict__ in, uint64_t ncols, uint6
     }
     const gl_t *cap = cap_in ? cap_in + row * out_pitch : nullptr;
     gl_t x[12];
-    const bool bf = pos_leaf_row<LOCKSTEP, DEFER>(x, p, ncols, vec16 != 0, cap, xs);
+    const bool bf = pos_leaf_row<LOCKSTEP, DEFER, SYNC>(x, p, ncols, vec16 != 0, cap, xs);
     if (DEFER && bf) {                            // before any store: cap_in may alias out
-        pos_leaf_row_exact(o, p, ncols, vec16, cap, xs);
+        if (live) pos_leaf_row_exact(o, p, ncols, vec16, cap, xs);
         return;
     }
     if (live) {
