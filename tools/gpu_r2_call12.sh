@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU call 12b: chunk size with the CTA barrier per permutation; 660- and 64-column rows
+# round 2, GPU call 12d: fold product on the ALU pipe instead of an IMAD.WIDE (rebalancing the pipes at +10 % instructions)
 mkdir -p gpurun_out
 cd tools/ubench/posv
-for v in s3_128 s4_128 s5_128 s6_128 s4_64; do for w in 660 64 100; do timeout 120 ./$v 4194304 $w "$v w$w"; done; done 2>&1 | tee ../../../gpurun_out/r02_pos_sync2.txt
+for v in d5 f3; do timeout 120 ./$v 4194304 660 "$v w660"; done 2>&1 | tee ../../../gpurun_out/r02_pos_sync4.txt

@@ -322,9 +322,28 @@ GL_HD void gl_borrow_note2(GlBorrow &bf, uint32_t wa, uint32_t wb) { bf.zmin = g
 template <bool PRODUCT>
 GL_HD gl_t gl_fold_defer_raw(gl_t lo, gl_t hi, uint32_t &w)
 {
-    constexpr bool V2 = PRODUCT && GL_FOLD_WIDE == 2;
+    constexpr bool V2 = PRODUCT && GL_FOLD_WIDE >= 2;
 #if GL_DEVICE_PTX
     gl_t r;
+    if (V2 && GL_FOLD_WIDE == 3) {                               // form 2 with p2*EPS = (p2 << 32) - p2 on the ALU pipe (experiment)
+        asm("{\n\t"
+            ".reg .u32 p0,p1,p2,p3,m,e0,e1;\n\t"
+            "mov.b64 {p0,p1}, %2;\n\t"
+            "mov.b64 {p2,p3}, %3;\n\t"
+            "sub.cc.u32 e0, 0, p2;\n\t"
+            "subc.u32 e1, p2, 0;\n\t"
+            "add.cc.u32 p0, p0, e0;\n\t"
+            "addc.cc.u32 p1, p1, e1;\n\t"
+            "addc.u32 m, 0, 0;\n\t"
+            "mov.b32 %1, p1;\n\t"
+            "add.u32 p3, p3, m;\n\t"
+            "sub.cc.u32 p0, p0, p3;\n\t"
+            "subc.u32 p1, p1, 0;\n\t"
+            "add.u32 p1, p1, m;\n\t"
+            "mov.b64 %0, {p0,p1};\n\t"
+            "}" : "=l"(r), "=r"(w) : "l"(lo), "l"(hi));
+        return r;
+    }
     if (V2) {
         asm("{\n\t"
             ".reg .u32 p0,p1,p2,p3,m;\n\t"
