@@ -149,6 +149,19 @@ int glp_merkle_group_proof(glp_ctx *ctx, uint64_t *proof, const uint64_t *source
  * idx is a host array; source and nodes are both device or both host memory; proofs may be either when they are device. */
 int glp_merkle_group_proofs(glp_ctx *ctx, uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width,
                             uint64_t height, const uint64_t *idx, uint64_t nidx);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  glp_merkle_group_proofs with the staged
+ * query indices kept in a file-scope device array of GLP_GROUP_PROOFS_STATIC_MAX entries (32 KiB, held by every GPU that
+ * loads the library until exit) instead of the context's growable scratch: it calls no cudaMalloc / cudaFree and no
+ * allocating library routine.  proofs, source and nodes must be DEVICE memory (the caller owns inputs and outputs), idx is a
+ * host array; nidx > GLP_GROUP_PROOFS_STATIC_MAX is rejected with GLP_E_ARG.  nidx == 0 performs only the per-device set-up
+ * (the array's address is looked up once per device), so it can be done ahead of time.  All calls on one device share the
+ * array, which keeps the previous call's indices (each call overwrites the entries it reads; nothing needs zeroing): calls
+ * that overlap on the GPU -- two contexts or streams of one device -- race; issue them one after another.  Returns with
+ * the context's stream idle. */
+#define GLP_GROUP_PROOFS_STATIC_MAX 4096
+int glp_merkle_group_proofs_static(glp_ctx *ctx, uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width,
+                                   uint64_t height, const uint64_t *idx, uint64_t nidx);
 
 /* ---- the fused hot path: Starks::genProof step 1 (src/starkpil/starks.cpp:53-57) ----
  * out_ext = extendPol(in), tree = merkletree(out_ext), root = last 4 words of tree, with no host round trip

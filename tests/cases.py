@@ -434,6 +434,59 @@ def check_group_proofs(ctx, reference, rng, device=True, shapes=((256, 21), (1 <
         del canon
 
 
+def check_group_proofs_static(ctx, rng, shapes=((1 << 10, 21), (64, 128), (2, 5), (1, 9)), limit=4096):
+    """glp_merkle_group_proofs_static (index staging in a fixed file-scope device array, no allocation) against the existing
+    glp_merkle_group_proofs on the same device-resident tree: two calls in a row per shape, the second with FEWER indices than
+    the first so that the array still holds stale entries of the call before; then the limit and the argument checks."""
+    from xlayer_prover_b200 import GlpError
+    ctx.merkle_group_proofs_static(None, None, None, 0, 1, np.zeros(0, dtype=np.uint64))      # nidx == 0: set-up only
+    for h, w in shapes:
+        src = edge_matrix(rng, h, w)
+        dsrc = ctx.to_device(src)
+        dnodes = ctx.device_alloc(8 * tree_words(h))
+        ctx.merkletree(dnodes, dsrc, w, h)
+        depth = int(h).bit_length() - 1
+        words = w + 4 * depth
+        for nidx in (min(limit, 300), 7):
+            idx = np.array([0, h - 1, h // 2] + [int(x) for x in rng.integers(0, h, size=nidx - 3)], dtype=np.uint64)
+            want = np.zeros((nidx, words), dtype=np.uint64)
+            ctx.merkle_group_proofs(want, dsrc, dnodes, w, h, idx)
+            dgot = ctx.device_alloc(8 * nidx * words)
+            ctx.memcpy(dgot, np.full(nidx * words, 0xDEADBEEF, dtype=np.uint64), 8 * nidx * words)
+            ctx.merkle_group_proofs_static(dgot, dsrc, dnodes, w, h, idx)
+            check_equal(ctx.to_host(dgot, (nidx, words)), want, "static group proofs %dx%d, %d indices" % (h, w, nidx))
+            ctx.device_free(dgot)
+        ctx.device_free(dsrc)
+        ctx.device_free(dnodes)
+    # the limit itself is accepted, one more is refused before anything is touched
+    h, w = 1 << 8, 4
+    src = edge_matrix(rng, h, w)
+    dsrc = ctx.to_device(src)
+    dnodes = ctx.device_alloc(8 * tree_words(h))
+    ctx.merkletree(dnodes, dsrc, w, h)
+    words = w + 4 * 8
+    idx = rng.integers(0, h, size=limit + 1, dtype=np.uint64)
+    dgot = ctx.device_alloc(8 * (limit + 1) * words)
+    want = np.zeros((limit, words), dtype=np.uint64)
+    ctx.merkle_group_proofs(want, dsrc, dnodes, w, h, idx[:limit])
+    ctx.merkle_group_proofs_static(dgot, dsrc, dnodes, w, h, idx[:limit])
+    check_equal(ctx.to_host(dgot, (limit, words)), want, "static group proofs at the limit")
+    for bad in (lambda: ctx.merkle_group_proofs_static(dgot, dsrc, dnodes, w, h, idx),                       # limit + 1 indices
+                lambda: ctx.merkle_group_proofs_static(np.zeros((4, words), dtype=np.uint64), dsrc, dnodes, w, h, idx[:4]),  # host output
+                lambda: ctx.merkle_group_proofs_static(dgot, dsrc, dnodes, w, h, np.array([h], dtype=np.uint64))):         # index out of range
+        try:
+            bad()
+        except GlpError as e:
+            assert e.code == -1, e
+        else:
+            raise AssertionError("glp_merkle_group_proofs_static accepted a bad call")
+    # a refused call leaves the library usable
+    ctx.merkle_group_proofs_static(dgot, dsrc, dnodes, w, h, idx[:5])
+    check_equal(ctx.to_host(dgot, (5, words)), want[:5], "static group proofs after refused calls")
+    for p_ in (dgot, dsrc, dnodes):
+        ctx.device_free(p_)
+
+
 def check_fri_prove(ctx, reference, rng, pol_bits=9, steps=(9, 6, 3), nq=6, widths=(5, 3, 9, 6, 2)):
     """The reference's WHOLE FRIProve::prove (src/starkpil/fri/friProve.cpp:5-190, compiled from the reference with its own
     Polinomial, FRIProof, Transcript and MerkleTreeGL: oracle/_ref/libfriref.so) against the same protocol driven through this

@@ -103,6 +103,8 @@ cudaError_t cudaSetDevice(int d);
 cudaError_t cudaGetDevice(int *d);
 cudaError_t cudaMemGetInfo(size_t *free_, size_t *total);
 cudaError_t cudaPointerGetAttributes(cudaPointerAttributes *a, const void *p);
+// a "device symbol" is a plain host variable here
+template <class T> static inline cudaError_t cudaGetSymbolAddress(void **p, T &sym) { *p = (void *)&sym; return cudaSuccess; }
 // IPC inside one process: the "handle" is the pointer itself (enough to exercise export/import/scatter on the CPU)
 struct cudaIpcMemHandle_t { char reserved[64]; };
 enum { cudaIpcMemLazyEnablePeerAccess = 1 };

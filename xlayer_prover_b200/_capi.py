@@ -57,6 +57,7 @@ SIGNATURES = {
     "glp_tree_num_elements": (u64, [u64]),
     "glp_merkle_group_proofs": (i32, [vp, vp, vp, vp, u64, u64, vp, u64]),
     "glp_merkle_group_proof": (i32, [vp, vp, vp, vp, u64, u64, u64]),
+    "glp_merkle_group_proofs_static": (i32, [vp, vp, vp, vp, u64, u64, vp, u64]),
     "glp_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64]),
     "glp_quotient_commit": (i32, [vp, vp, vp, vp, vp, u64, u64, u64, u64]),
     "glp_const_tree_num_elements": (u64, [u64, u64]),
@@ -273,6 +274,13 @@ class Context:
         """getGroupProof for every index of `idx` (a host uint64 array) in one launch / one download"""
         idx = np.ascontiguousarray(idx, dtype=np.uint64)
         self.lib.check(self.lib.glp_merkle_group_proofs(self.h, ptr_of(proofs), ptr_of(source), ptr_of(nodes), width, height, ptr_of(idx), idx.size))
+
+    def merkle_group_proofs_static(self, proofs, source, nodes, width, height, idx):
+        """merkle_group_proofs with the index staging in a fixed device array: no allocation; device buffers, at most
+        GLP_GROUP_PROOFS_STATIC_MAX (4096) indices"""
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        self.lib.check(self.lib.glp_merkle_group_proofs_static(self.h, ptr_of(proofs), ptr_of(source), ptr_of(nodes), width, height, ptr_of(idx),
+                                                               idx.size))
 
     def commit(self, out_ext, tree, inp, n, n_ext, ncols):
         root = np.zeros(4, dtype=np.uint64)

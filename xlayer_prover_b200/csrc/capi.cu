@@ -12,6 +12,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1943,6 +1944,70 @@ extern "C" int glp_measure_pipe_peaks(glp_ctx *ctx, double ops_per_s[5])
 {
     if (!ctx || !ops_per_s) return fail(GLP_E_ARG, "glp_measure_pipe_peaks: NULL argument");
     return measure_pipe_modes(ctx, ops_per_s, 5);
+}
+
+// ------------------------------------------------------------------------------------------------
+// batched group proofs without any allocation (glp_merkle_group_proofs_static)
+// ------------------------------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  glp_merkle_group_proofs stages the query
+// indices in ctx->tmp_out, which ensure() may cudaMalloc / cudaFree; here that scratch is a file-scope device array of a
+// fixed size, GLP_GROUP_PROOFS_STATIC_MAX indices (32 KiB), which every GPU that loads the library holds until exit.
+// In host code `g_gp_static_idx` is only the host-side stand-in for the symbol, never a device address: the address the
+// kernel gets comes from cudaGetSymbolAddress, asked once per device with that device current (gp_static_scratch).
+// Every call on a device shares the array and the array keeps the last call's indices; a call overwrites the first nidx
+// entries and the kernel reads only those, so nothing has to start at zero -- but two calls that overlap on the GPU
+// (different streams, different contexts of one device) race on it.
+static __device__ __align__(256) unsigned long long g_gp_static_idx[GLP_GROUP_PROOFS_STATIC_MAX];
+
+namespace {
+constexpr int GP_STATIC_MAX_DEVICES = 64;
+std::mutex g_gp_static_mu;
+uint64_t *g_gp_static_addr[GP_STATIC_MAX_DEVICES];     // per device: the device address of g_gp_static_idx
+
+int gp_static_scratch(int device, uint64_t **out)      // the caller has made `device` current
+{
+    if (device < 0 || device >= GP_STATIC_MAX_DEVICES) return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: device index out of range");
+    std::lock_guard<std::mutex> lk(g_gp_static_mu);
+    if (!g_gp_static_addr[device]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_gp_static_idx);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(GLP_E_CUDA, std::string("glp_merkle_group_proofs_static: cudaGetSymbolAddress failed (") + cudaGetErrorString(e) + ")");
+        }
+        g_gp_static_addr[device] = (uint64_t *)p;
+    }
+    *out = g_gp_static_addr[device];
+    return GLP_OK;
+}
+}  // namespace
+
+extern "C" int glp_merkle_group_proofs_static(glp_ctx *ctx, uint64_t *proofs, const uint64_t *source, const uint64_t *nodes, uint64_t width,
+                                              uint64_t height, const uint64_t *idx, uint64_t nidx)
+{
+    if (!ctx) return fail(GLP_E_ARG, "ctx is NULL");
+    if (nidx > GLP_GROUP_PROOFS_STATIC_MAX)
+        return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: " + std::to_string(nidx) + " indices exceed the static scratch (" +
+                                   std::to_string((unsigned long long)GLP_GROUP_PROOFS_STATIC_MAX) + "); use glp_merkle_group_proofs");
+    CU(cudaSetDevice(ctx->device));
+    uint64_t *didx = nullptr;
+    GLP(gp_static_scratch(ctx->device, &didx));
+    if (nidx == 0) return GLP_OK;                                // set-up only: lets a caller do it before a capture begins
+    if (!proofs || !nodes || !idx || (!source && width)) return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: NULL pointer");
+    if (!is_pow2(height)) return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: height must be a power of two");
+    if (on_device(idx)) return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: idx is a host array");
+    if (!on_device(proofs) || !on_device(nodes) || (width && !on_device(source)))
+        return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: proofs, source and nodes must be device memory (no staging buffer is allocated)");
+    for (uint64_t q = 0; q < nidx; q++)
+        if (idx[q] >= height) return fail(GLP_E_ARG, "glp_merkle_group_proofs_static: index out of range");
+    const uint64_t words = width + 4 * ilog2_u64(height);
+    CU(cudaMemcpyAsync(didx, idx, nidx * sizeof(uint64_t), cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_group_proofs, (unsigned)nidx, 128, 0, (gl_t *)proofs, words, (const gl_t *)source, (const gl_t *)nodes, width, height,
+           (const uint64_t *)didx, nidx);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    return GLP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------
