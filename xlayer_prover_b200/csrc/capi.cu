@@ -60,6 +60,8 @@ struct glp_ctx {
     uint64_t launches = 0;
     uint64_t scratch_limit = 0;
     uint64_t stream_cols = 160;              // column-block width of the streamed (host-pointer) commit; GLP_STREAM_COLS
+    uint32_t stream_grow = 200;              // graded first blocks of the streamed commit, percent per step (0: one short block, then equal); GLP_STREAM_GROW
+    std::vector<uint64_t> stream_plan;       // explicit block widths in columns; GLP_STREAM_PLAN
     uint32_t max_logq = NTT_MAX_LOGQ;        // tile size cap; GLP_NTT_MAX_LOGQ lowers it so tests reach the multi-pass paths at small sizes
     bool no_pass_tables = false;             // GLP_NTT_NO_PASS_TABLES=1: two-level twiddle/scale tables only (the path sizes > 2^25 take)
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
@@ -225,6 +227,16 @@ extern "C" int glp_init(int device, glp_ctx **out)
     if (ds && atoi(ds) >= 1 && atoi(ds) <= 2) ctx->d2h_split = (uint32_t)atoi(ds);
     const char *sc = getenv("GLP_STREAM_COLS");
     if (sc && atoi(sc) >= 8) ctx->stream_cols = (uint64_t)(atoi(sc) / 8) * 8;
+    const char *sg = getenv("GLP_STREAM_GROW");
+    if (sg && (atoi(sg) == 0 || atoi(sg) > 100)) ctx->stream_grow = (uint32_t)atoi(sg);
+    if (const char *sp = getenv("GLP_STREAM_PLAN"))
+        for (const char *q = sp; *q;) {
+            char *end = nullptr;
+            const long v = strtol(q, &end, 10);
+            if (end == q) break;
+            if (v >= 8) ctx->stream_plan.push_back((uint64_t)v);
+            q = (*end == ',') ? end + 1 : end;
+        }
     *out = ctx;
     return GLP_OK;
 }
@@ -1379,6 +1391,49 @@ extern "C" int glp_merkle_group_proofs(glp_ctx *ctx, uint64_t *proofs, const uin
 // ------------------------------------------------------------------------------------------------
 // fused commit
 // ------------------------------------------------------------------------------------------------
+// Column-block boundaries of the streamed commit: col0[0] = 0 < ... < col0[nblocks] = ncols, every boundary but the last a
+// multiple of 8 (whole sponge blocks), no block wider than wmax.
+//   * GLP_STREAM_PLAN="32,48,72,..." gives the widths (the last one repeats until the columns are used up);
+//   * GLP_STREAM_GROW=0 is the round-1 layout: one short first block (32 columns), then equal blocks;
+//   * default (GLP_STREAM_GROW=200): a graded start -- 32, 64, 128 columns, each block twice the one before until wmax is
+//     reached or half of the rest is used -- then equal blocks (660 columns: 32, 64, 128, 152, 144, 140).  The download is the
+//     longest stream of the pipeline (2 x the upload's bytes over the same link) and block k's download can only start when
+//     block k's LDE is done, which waits for block k's upload: with equal 160-column blocks the download link idles for most
+//     of the first 0.35 s.  Measured at 2^23 x 660 on one box (profiles/r02_e2e_plan.txt): 1983 ms equal blocks, 1934 ms
+//     graded x2, 1928 ms for 32,64,96,160,160,148, 1982-1997 ms for finer starts (x1.5: 32,48,72,112,...) whose narrow
+//     blocks cost LDE lanes and short copy rows.  What is left is the link: 133 GB both ways at 82-86 GB/s (2-D + 2-D) while
+//     the upload runs, 49.5 GB/s for the download alone afterwards (profiles/r01_pcie_probe.txt).
+//     A short LAST block would only be copied in short, slow rows (160-byte rows move at 18 GB/s, 768-byte rows at 46-52 GB/s),
+//     so the tail stays equal.
+static std::vector<uint64_t> stream_block_plan(const glp_ctx *ctx, uint64_t ncols, uint64_t wmax)
+{
+    const uint64_t units = (ncols + 7) / 8, wu = wmax / 8 ? wmax / 8 : 1;
+    std::vector<uint64_t> u;                                                 // block sizes in units of 8 columns
+    uint64_t rem = units;
+    if (!ctx->stream_plan.empty()) {
+        for (size_t i = 0; rem; i++) {
+            uint64_t x = ctx->stream_plan[i < ctx->stream_plan.size() ? i : ctx->stream_plan.size() - 1] / 8;
+            x = x < 1 ? 1 : (x > wu ? wu : x);
+            x = x > rem ? rem : x;
+            u.push_back(x);
+            rem -= x;
+        }
+    } else {
+        if (ctx->stream_grow == 0) {
+            if (units > 2 * wu && wu > 4) { u.push_back(4); rem -= 4; }
+        } else {
+            for (uint64_t x = 4; x < wu && rem >= 2 * x; x = (x * ctx->stream_grow + 99) / 100) { u.push_back(x); rem -= x; }
+        }
+        const uint64_t nrest = rem ? (rem + wu - 1) / wu : 0;
+        for (uint64_t k = 0; k < nrest; k++) u.push_back(rem / nrest + (k < rem % nrest ? 1 : 0));
+    }
+    std::vector<uint64_t> col0(u.size() + 1);
+    col0[0] = 0;
+    for (size_t k = 0; k < u.size(); k++) col0[k + 1] = (col0[k] + 8 * u[k] < ncols) ? col0[k] + 8 * u[k] : ncols;
+    col0.back() = ncols;
+    return col0;
+}
+
 // Host input: the commit as a software pipeline over column blocks of `w` columns (a multiple of 8, so every
 // sponge block of the leaf hash has one owner).  Per block k:
 //     copy stream 0 : upload block k (strided 2-D copy out of the row-major host matrix)
@@ -1413,28 +1468,11 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
         // PCIe link with an upload for the first 0.85 s only (2-D downloads: 43 GB/s next to an upload, 47 GB/s alone).
         full_stage = ctx->stage_all && 8 * n * (ncols + 8) + (w + 8) * (per_col - 16 * n) <= budget;
     }
-    // Blocks in units of 8 columns.  The first block is short (32 columns) so that the GPU starts after a short
-    // upload -- nothing overlaps the first upload; the rest are equal (a short LAST block would only be copied in
-    // short, slow rows: 160-byte rows move at 18 GB/s, 768-byte rows at 46-52 GB/s, profiles/r01_pcie_probe.txt).
-    const uint64_t units = (ncols + 7) / 8;
-    const uint64_t wu = w / 8;                                              // units per full block
-    const uint64_t first = (units > 2 * wu && wu > 4) ? 4 : 0;             // units of the short first block
-    const uint64_t rest = units - first;
-    uint64_t nrest = (rest + wu - 1) / wu;
-    if (nrest < 1) nrest = 1;
-    const uint64_t ub = rest / nrest, extra = rest % nrest;                 // the first `extra` equal blocks get ub+1 units
-    const uint64_t nblocks = nrest + (first ? 1 : 0);
-    w = (ub + (extra ? 1 : 0)) * 8;                                          // widest block: sizes the buffers
-    std::vector<uint64_t> col0(nblocks + 1);
-    col0[0] = 0;
-    for (uint64_t k = 0; k < nblocks; k++) {
-        uint64_t u;
-        if (first && k == 0) u = first;
-        else { const uint64_t kk = k - (first ? 1 : 0); u = ub + (kk < extra ? 1 : 0); }
-        const uint64_t c1 = col0[k] + u * 8;
-        col0[k + 1] = c1 < ncols ? c1 : ncols;
-    }
-    col0[nblocks] = ncols;
+    const std::vector<uint64_t> col0 = stream_block_plan(ctx, ncols, w);
+    const uint64_t nblocks = col0.size() - 1;
+    w = 0;                                                                   // widest block: sizes the buffers
+    for (uint64_t k = 0; k < nblocks; k++) w = (col0[k + 1] - col0[k] > w) ? col0[k + 1] - col0[k] : w;
+    w = (w + 7) / 8 * 8;
     GLP(ensure(ctx, ctx->tmp_in, (full_stage ? (size_t)n * (col0[nblocks] + 8) : 2 * (size_t)n * w) * sizeof(gl_t)));
     if (!ext_dev) GLP(ensure(ctx, ctx->tmp_out, 2 * (size_t)n_ext * w * sizeof(gl_t)));
     // the LDE scratch for the WIDEST block, before the streams fork: lde_block's own ensure() would otherwise free and
@@ -1514,7 +1552,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
     cudaError_t e0 = cudaStreamSynchronize(ctx->stream), e1 = cudaStreamSynchronize(ctx->copy_stream[0]),
                 e2 = cudaStreamSynchronize(ctx->copy_stream[1]);
     if (ctx->trace && e0 == cudaSuccess && e1 == cudaSuccess && e2 == cudaSuccess) {
-        fprintf(stderr, "[glp trace] streamed commit: %llu blocks of %llu columns; ms since start: block  uploaded  extended  hashed  downloaded\n",
+        fprintf(stderr, "[glp trace] streamed commit: %llu blocks of at most %llu columns; ms since start: block  uploaded  extended  hashed  downloaded\n",
                 (unsigned long long)nblocks, (unsigned long long)w);
         for (uint64_t k = 0; k < nblocks; k++) {
             float t[4] = {-1, -1, -1, -1};
@@ -1522,7 +1560,7 @@ static int commit_streamed(glp_ctx *ctx, uint64_t *out_ext, bool ext_dev, uint64
             cudaEventElapsedTime(&t[1], start, lde_done[k]);
             if (want_tree) cudaEventElapsedTime(&t[2], start, hashed[k]);
             if (want_ext && !ext_dev) cudaEventElapsedTime(&t[3], start, down[k]);
-            fprintf(stderr, "[glp trace] %3llu %9.1f %9.1f %9.1f %9.1f\n", (unsigned long long)k, t[0], t[1], t[2], t[3]);
+            fprintf(stderr, "[glp trace] %3llu %9.1f %9.1f %9.1f %9.1f   (%u columns)\n", (unsigned long long)k, t[0], t[1], t[2], t[3], width(k));
         }
         cudaGetLastError();
     }
