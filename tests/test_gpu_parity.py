@@ -510,6 +510,26 @@ def test_narrow_equals_wide_mapping(ctx, rng):
         wide.close()
 
 
+@pytest.mark.parametrize("ncols", [37, 48, 56, 60, 80, 88, 165])
+def test_remainder_column_group_split(ctx, oracle, rng, ncols):
+    """32 k + r columns (a rank's slice of 660 columns on 4 / 8 devices: 165 / 80-88): the remainder columns of every NTT pass run
+    as their own launch on the narrow mapping.  Against the oracle (NTT, INTT, extension, commit) and against the one-launch
+    layout (GLP_NTT_NO_SPLIT=1), at three-pass sizes."""
+    a = edge_matrix(rng, 1 << 13, ncols)
+    check_ntt(ctx, oracle, a)
+    check_equal(run_extend(ctx, a, 1 << 15, device=True), oracle.extend_pol(a, 1 << 15), "extend %d columns" % ncols)
+    b = edge_matrix(rng, 1 << 17, ncols)
+    whole = env_ctx(GLP_NTT_NO_SPLIT=1)
+    try:
+        check_equal(run_extend(ctx, b, 1 << 18, device=True), run_extend(whole, b, 1 << 18, device=True), "split vs one launch, %d columns" % ncols)
+        got = run_commit(ctx, b, 1 << 18, device=True)
+        want = run_commit(whole, b, 1 << 18, device=True)
+        for g, w in zip(got, want):
+            check_equal(g, w, "commit, split vs one launch, %d columns" % ncols)
+    finally:
+        whole.close()
+
+
 # ---------------------------------------------------------------- the callers either side of the commit (SURVEY 8f)
 def test_quotient_commit(ctx, reference, rng):
     """Starks::genProof step 4 (starks.cpp:261-291) at test sizes and at a zkEVM-like shape (qDim 3, qDeg 2, blowup 2)"""

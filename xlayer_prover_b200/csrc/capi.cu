@@ -67,6 +67,7 @@ struct glp_ctx {
     bool trace = false;                      // GLP_TRACE=1: timeline of the streamed commit on stderr
     uint64_t merkle_stream_min = 0;          // GLP_MERKLE_STREAM_MIN: bytes from which a host-resident Merkle source is uploaded block by block (tests lower it)
     bool stage_all = true;                   // GLP_STAGE_ALL=0: two alternating upload buffers even when the whole input fits
+    bool no_split = false;                   // GLP_NTT_NO_SPLIT=1: the remainder column group of a wide matrix stays on the lane = column mapping
     bool no_narrow = false;                  // GLP_NTT_NO_NARROW=1: lane = column even for matrices of <= 16 columns (comparison runs)
     // optimistic NTT passes (k_ntt_pass_opt): the device-resident LDE runs them and is repeated with the exact passes when
     // the flag they raise is set (dev_extend_pol_checked)
@@ -213,6 +214,8 @@ extern "C" int glp_init(int device, glp_ctx **out)
     ctx->no_fused_lde = nfl && atoi(nfl) != 0;
     const char *nn = getenv("GLP_NTT_NO_NARROW");
     ctx->no_narrow = nn && atoi(nn) != 0;
+    const char *nsp = getenv("GLP_NTT_NO_SPLIT");
+    ctx->no_split = nsp && atoi(nsp) != 0;
     const char *no = getenv("GLP_NTT_OPT");
     if (no) ctx->opt_enabled = atoi(no) != 0;
     const char *nfr = getenv("GLP_NTT_FORCE_RETRY");
@@ -499,6 +502,27 @@ static int get_scale_table(glp_ctx *ctx, uint32_t logN, const NttPlanLogs &pl, c
 template <int A, int B>
 static int launch_pass_ab(glp_ctx *ctx, const NttPass &a_in, bool inv, uint32_t lsh)
 {
+    // A matrix of 32 k + r columns leaves 32 - r lanes of its last column group idle (a rank's slice of 660 columns on 4 / 8
+    // devices is 165 / 80-88 columns wide: 5 / 16 / 24 columns in the last group).  The remainder runs as its own launch on the
+    // NARROW mapping instead -- 2^log_cw >= r lanes per tile, 32 >> log_cw row tiles per warp -- when that takes fewer warps:
+    // r <= 16 in one launch; 16 < r <= 24 as 16 columns plus r - 16 <= 8 columns (1/2 + 1/4 of a group).  The launches touch
+    // disjoint columns; passes are in place per column, so their order does not matter.  GLP_NTT_NO_SPLIT=1 turns it off.
+    if (!ctx->no_narrow && !ctx->no_split && !ctx->co_active && a_in.ncols > NTT_LANES) {
+        const uint32_t r = a_in.ncols % NTT_LANES;
+        uint32_t tail = 0;                                        // columns handed to a launch of their own
+        if (r && r <= NTT_NARROW_MAX_COLS) tail = r;
+        else if (r > 16 && r <= 24) tail = r - 16;
+        if (tail) {
+            NttPass head = a_in, rest = a_in;
+            head.ncols = a_in.ncols - tail;
+            rest.ncols = tail;
+            rest.in += head.ncols;
+            rest.out += head.ncols;
+            rest.part_col0 += head.ncols;
+            GLP((launch_pass_ab<A, B>(ctx, head, inv, lsh)));
+            return launch_pass_ab<A, B>(ctx, rest, inv, lsh);
+        }
+    }
     NttPass a = a_in;
     const bool narrow = a.ncols <= NTT_NARROW_MAX_COLS && !ctx->no_narrow;
     const uint64_t ntiles = 1ull << (a.logN - (A + B));
