@@ -178,12 +178,22 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
 {
     constexpr int QX = 1 << LOGX;
     if (mul) {
+        if (fptr) {                                              // table row: the pointer walks, no index arithmetic per element
+            uint64_t fa = (uint64_t)(fptr + ((uint64_t)t0 << fsh));
+            const uint64_t fstepb = ((uint64_t)tstride << fsh) * sizeof(gl_t);
 #pragma unroll
-        for (int w = 0; w < QX; w++) {
-            const uint32_t t = t0 + (uint32_t)w * tstride;
-            const gl_t f = fptr ? __ldg(fptr + ((uint64_t)t << fsh)) : ntt_factor_slow(sl, fkind, p, fbase + ((uint64_t)t << fbsh));
-            gl_t &x = v[ntt_slot<LOGX, INV>(w)];
-            x = gl_mul_fma(x, f);
+            for (int w = 0; w < QX; w++) {
+                gl_t &x = v[ntt_slot<LOGX, INV>(w)];
+                x = gl_mul_fma(x, __ldg((const gl_t *)fa));
+                fa += fstepb;
+            }
+        } else {
+#pragma unroll
+            for (int w = 0; w < QX; w++) {
+                const uint32_t t = t0 + (uint32_t)w * tstride;
+                gl_t &x = v[ntt_slot<LOGX, INV>(w)];
+                x = gl_mul_fma(x, ntt_factor_slow(sl, fkind, p, fbase + ((uint64_t)t << fbsh)));
+            }
         }
     }
     if (a.canon_out) {
@@ -201,10 +211,13 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
         }
         return;
     }
-    gl_t *o = a.out + (rbase + ((uint64_t)t0 << rsh)) * a.out_pitch + col;
-    const uint64_t step = ((uint64_t)tstride << rsh) * a.out_pitch;
+    uint64_t oa = (uint64_t)(a.out + (rbase + ((uint64_t)t0 << rsh)) * a.out_pitch + col);
+    const uint64_t stepb = ((uint64_t)tstride << rsh) * a.out_pitch * sizeof(gl_t);
 #pragma unroll
-    for (int w = 0; w < QX; w++) o[(uint64_t)w * step] = v[ntt_slot<LOGX, INV>(w)];
+    for (int w = 0; w < QX; w++) {
+        *(gl_t *)oa = v[ntt_slot<LOGX, INV>(w)];
+        oa += stepb;
+    }
 }
 
 // One tile pass.  A, B: log2 radix of the two in-register steps (B == 0: single step, no shared memory).
@@ -269,12 +282,23 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
     for (uint32_t b = (B == 0 ? 0 : warp); b < (uint32_t)QB; b += nwarps) {
         gl_t v[QA];
         {
+            // input m is row r0 + m * 2^(B + logS) of the sub-transform; rows >= a.live are zero and never read.  The count of
+            // live inputs is worked out once and the pointer walks by in_step: a 64-bit compare, a 64-bit multiply and an LEA
+            // pair per element otherwise (12 of the 150 instructions per element and pass).
             const uint64_t r0 = ((uint64_t)b << logS) + p;       // input row of m = 0 inside the sub-transform
             const gl_t *in = a.in + ((bb << a.log_in_L) + r0) * a.in_pitch + col;
-            const uint64_t rstep = (uint64_t)QB << logS;
+            uint32_t nlive = 0;
+            if (colok && r0 < a.live) {
+                const uint64_t k = ((a.live - r0 - 1) >> (B + logS)) + 1;
+                nlive = k < (uint64_t)(QA >> LSH) ? (uint32_t)k : (uint32_t)(QA >> LSH);
+            }
+            uint64_t addr = (uint64_t)in;                        // byte address: one 64-bit add per element (an element index costs an LEA pair more)
+            const uint64_t stepb = in_step * sizeof(gl_t);
 #pragma unroll
-            for (int m = 0; m < (QA >> LSH); m++)
-                v[m] = (colok && r0 + (uint64_t)m * rstep < a.live) ? in[(uint64_t)m * in_step] : 0;   // plain load: middle passes run in place
+            for (int m = 0; m < (QA >> LSH); m++) {
+                v[m] = (uint32_t)m < nlive ? *(const gl_t *)addr : 0;   // plain load: middle passes run in place
+                addr += stepb;
+            }
         }
         if (a.mask) {                                            // see NTT_MASK: x -> x*R, undone by the INTT's scale table
 #pragma unroll
@@ -284,11 +308,16 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
             for (int m = 0; m < (QA >> LSH); m++) v[m] = gl_canon(v[m]);
         }
         if (pre) {                                               // w_L^(+-p q)
+            // The table test stays OUTSIDE the loop: with `twp ? load : call` per element every load sits behind a branch, ptxas
+            // cannot hoist it, and the 16 table loads of a warp were issued and waited for one after another -- half of the time
+            // of a pass with pre-twiddles (ncu source page, profiles/r02_ntt_source_profile.txt).
+            if (twp) {
 #pragma unroll
-            for (int m = 0; m < (QA >> LSH); m++) {
-                const uint32_t q = (uint32_t)m * QB + b;
-                const gl_t f = twp ? __ldg(twp + q) : ntt_factor_slow(sl, INV ? NTT_F_TW_INV : NTT_F_TW, p, q);
-                v[m] = gl_mul_fma(v[m], f);
+                for (int m = 0; m < (QA >> LSH); m++) v[m] = gl_mul_fma(v[m], __ldg(twp + (uint32_t)m * QB + b));
+            } else {
+#pragma unroll
+                for (int m = 0; m < (QA >> LSH); m++)
+                    v[m] = gl_mul_fma(v[m], ntt_factor_slow(sl, INV ? NTT_F_TW_INV : NTT_F_TW, p, (uint32_t)m * QB + b));
             }
         }
         GlDefer f = {0, 0};
