@@ -694,9 +694,32 @@ GL_HD gl_t gl_fold_times_2p64(uint32_t w0, uint32_t w1, uint32_t w2)
 //   k <= 32      : a*2^k < 2^96                    -> gl_fold96                    (9 instructions with the shifts)
 //   32 < k <= 64 : the general fold                                               (15)
 //   k > 64       : (a * 2^(k-64)) * 2^64, 95 bits  -> gl_fold_times_2p64           (10; was 18)
+// GL_POW2_FMA 1 (device; off): the shift by k mod 32 as a multiplication by 2^(k mod 32) -- two IMAD.WIDE on the multiplier
+// pipe instead of three or four SHF on the ALU pipe, the busier one in the NTT passes (ALU 70-79 %, fmaheavy 41-47 %).  The
+// factor is read from the constant bank so that ptxas cannot turn the product back into shifts.  Measured: no change (LDE 313.4
+// against 313.7 ms) -- the passes run at the issue rate of their mix, not at a pipe limit; kept as a knob.
+#ifndef GL_POW2_FMA
+#define GL_POW2_FMA 0
+#endif
+#if defined(__CUDACC__) && !defined(GLP_EMU)
+static __constant__ uint32_t GL_POW2_OPAQUE[32] = {
+    1u << 0,  1u << 1,  1u << 2,  1u << 3,  1u << 4,  1u << 5,  1u << 6,  1u << 7,  1u << 8,  1u << 9,  1u << 10, 1u << 11, 1u << 12, 1u << 13, 1u << 14, 1u << 15,
+    1u << 16, 1u << 17, 1u << 18, 1u << 19, 1u << 20, 1u << 21, 1u << 22, 1u << 23, 1u << 24, 1u << 25, 1u << 26, 1u << 27, 1u << 28, 1u << 29, 1u << 30, 1u << 31};
+#endif
 GL_HD gl_t gl_mul_pow2(gl_t a, unsigned k)
 {
     if (k == 0) return a;
+#if GL_DEVICE_PTX && GL_POW2_FMA
+    if (k % 32 != 0 && k < 96) {
+        const uint32_t f = GL_POW2_OPAQUE[k % 32];
+        const uint64_t t = (uint64_t)(uint32_t)a * f;
+        const uint64_t u = (uint64_t)(uint32_t)(a >> 32) * f + (t >> 32);   // a * 2^(k % 32) = (u_hi : u_lo : t_lo), below 2^95
+        const uint32_t w0 = (uint32_t)t, w1 = (uint32_t)u, w2 = (uint32_t)(u >> 32);
+        if (k < 32) return gl_fold96(((gl_t)w1 << 32) | w0, w2);
+        if (k < 64) return gl_reduce128((gl_t)w0 << 32, ((gl_t)w2 << 32) | w1);
+        return gl_fold_times_2p64(w0, w1, w2);
+    }
+#endif
     if (k <= 32) return gl_fold96(a << k, (uint32_t)(a >> (64 - k)));
     if (k < 64) return gl_reduce128(a << k, a >> (64 - k));
     if (k == 64) return gl_reduce128(0, a);
