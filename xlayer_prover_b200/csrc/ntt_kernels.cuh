@@ -35,13 +35,20 @@
 
 #define NTT_MAX_LOGQ 8              // tile rows <= 2^8
 #define NTT_LOGT 12                 // two-level tables: low 12 bits / the rest
+// CTA shape: 8 warps, registers capped for 3 CTAs per SM (80 registers; three 64 KB tiles are what shared memory holds).  Round 1
+// ran 16 warps x 2 CTAs at 64 registers (8 x 3 was a tie then); once the table loads were no longer serialised behind branches
+// the extra 16 registers (fewer spills in the 16-point transforms) and the third tile in flight won: LDE 312.8 -> 302.9 ms
+// (profiles/r02_ntt_variants.txt).
 #ifndef NTT_WARPS
-#define NTT_WARPS 16
+#define NTT_WARPS 8
 #endif
 #ifndef NTT_MINBLOCKS
-#define NTT_MINBLOCKS 2              // CTAs per SM the register allocation is capped for (16 warps x 2: 64 registers)
+#define NTT_MINBLOCKS 3              // CTAs per SM the register allocation is capped for
 #endif
 #define NTT_LANES 32
+#ifndef NTT_LOAD_FAST
+#define NTT_LOAD_FAST 1              // a second, unpredicated copy of the tile loads for tiles whose inputs are all live (LDE -1 %)
+#endif
 #define NTT_THREADS (NTT_WARPS * NTT_LANES)
 #define NTT_MAX_PASSES 4
 
@@ -227,7 +234,7 @@ static __device__ __forceinline__ void ntt_store_outputs(const NttPass &a, const
 // are shared by 32/cw neighbouring tiles of cw = 2^log_cw >= ncols lanes each.  Neighbouring tiles are neighbouring rows
 // p, p+1, ..., so a warp still touches one contiguous run of memory per access; the tile index, and with it the twiddle
 // row, becomes a per-lane quantity instead of a warp-uniform one.  Everything else is the same code.
-// The body works on the tile(s) of virtual block index vbx with `nwarps` warps (k_ntt_pass: vbx = blockIdx.x, 16 warps;
+// The body works on the tile(s) of virtual block index vbx with `nwarps` warps (k_ntt_pass: vbx = blockIdx.x, NTT_WARPS warps;
 // k_ntt_pass_co: a small resident grid walks the block indices, see below).
 template <int A, int B, bool INV, int LSH, bool NARROW, bool OPT = false>
 static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *tile, const uint32_t vbx, const uint32_t nwarps)
@@ -294,10 +301,21 @@ static __device__ __forceinline__ void ntt_pass_block(const NttPass &a, gl_t *ti
             }
             uint64_t addr = (uint64_t)in;                        // byte address: one 64-bit add per element (an element index costs an LEA pair more)
             const uint64_t stepb = in_step * sizeof(gl_t);
+#if NTT_LOAD_FAST
+            if (nlive == (uint32_t)(QA >> LSH)) {                // every input live (all passes but a zero-padded first one): no predicates, no zero-fill
 #pragma unroll
-            for (int m = 0; m < (QA >> LSH); m++) {
-                v[m] = (uint32_t)m < nlive ? *(const gl_t *)addr : 0;   // plain load: middle passes run in place
-                addr += stepb;
+                for (int m = 0; m < (QA >> LSH); m++) {
+                    v[m] = *(const gl_t *)addr;
+                    addr += stepb;
+                }
+            } else
+#endif
+            {
+#pragma unroll
+                for (int m = 0; m < (QA >> LSH); m++) {
+                    v[m] = (uint32_t)m < nlive ? *(const gl_t *)addr : 0;   // plain load: middle passes run in place
+                    addr += stepb;
+                }
             }
         }
         if (a.mask) {                                            // see NTT_MASK: x -> x*R, undone by the INTT's scale table
@@ -375,7 +393,7 @@ k_ntt_pass_opt(NttPass a)
     ntt_pass_block<A, B, INV, LSH, false, true>(a, tile, blockIdx.x, NTT_WARPS);
 }
 
-// Co-resident flavour (two-step tiles only): a grid of a few CTAs per SM, each of blockDim.x/32 <= 16 warps, walks
+// Co-resident flavour (two-step tiles only): a grid of a few CTAs per SM, each of blockDim.x/32 <= NTT_WARPS warps, walks
 // the `nvb` block indices of k_ntt_pass.  It is launched on a high-priority stream UNDER a running leaf-hash kernel
 // (commit_overlapped in capi.cu): its whole grid becomes resident as soon as hash CTAs retire, takes a fixed slice of
 // every SM (16 K registers and 64 KB of shared memory at 256 threads) and leaves the rest to the hash, so the LDE of
