@@ -518,6 +518,18 @@ def test_remainder_column_group_split(ctx, oracle, rng, ncols):
     a = edge_matrix(rng, 1 << 13, ncols)
     check_ntt(ctx, oracle, a)
     check_equal(run_extend(ctx, a, 1 << 15, device=True), oracle.extend_pol(a, 1 << 15), "extend %d columns" % ncols)
+    # guard bands around the output (compute-sanitizer is not available on the pool): the pointer-walking stores of every pass and
+    # launch must stay inside [out, out + n_ext * ncols)
+    n, n_ext, guard = 1 << 13, 1 << 15, 1 << 12
+    src = ctx.to_device(a)
+    buf = ctx.device_alloc(8 * (n_ext * ncols + 2 * guard))
+    ctx.memcpy(buf, np.full(n_ext * ncols + 2 * guard, 0xA5A5A5A5A5A5A5A5, dtype=np.uint64), 8 * (n_ext * ncols + 2 * guard))
+    ctx.extend_pol(buf + 8 * guard, src, n_ext, n, ncols)
+    got = ctx.to_host(buf, (n_ext * ncols + 2 * guard,))
+    assert (got[:guard] == 0xA5A5A5A5A5A5A5A5).all() and (got[-guard:] == 0xA5A5A5A5A5A5A5A5).all(), "extendPol wrote outside its output"
+    check_equal(got[guard:-guard].reshape(n_ext, ncols), oracle.extend_pol(a, n_ext), "extend into a guarded buffer")
+    ctx.device_free(src)
+    ctx.device_free(buf)
     b = edge_matrix(rng, 1 << 17, ncols)
     whole = env_ctx(GLP_NTT_NO_SPLIT=1)
     try:
