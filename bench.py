@@ -455,6 +455,9 @@ def main_ours(args):
                                "achieved": leaf_pps * POS_SASS["instructions"] if leaf_pps else None,
                                "peak": int_peak["interleaved_lane_ops_per_s"], "unit": "lane-instructions/s",
                                "frac": leaf_pps * POS_SASS["instructions"] / int_peak["interleaved_lane_ops_per_s"] if leaf_pps else None,
+                               # IMAD.WIDE is a half-rate instruction (measured alone at half the IMAD rate): counted as two issue slots
+                               "frac_imad_wide_as_two_slots": leaf_pps * (POS_SASS["instructions"] + POS_SASS["imad_wide"]) / int_peak["interleaved_lane_ops_per_s"]
+                               if leaf_pps else None,
                                "note": "the B200 issues ~70 integer lane-instructions per clock per SM whatever the IMAD/ALU mix (IMAD alone 60, IADD3 alone 61, "
                                        "interleaved 70): the kernel's stream runs at that rate, so only a shorter stream makes it faster"},
             "measured_lane_ops_per_s": int_peak,
